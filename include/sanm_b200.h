@@ -1,0 +1,224 @@
+/* include/sanm_b200.h -- C ABI of libsanm_b200.so, the B200-native (sm_100a,
+ * FP64) implementation of SANM's ANM inner loop.
+ *
+ * This is the drop-in boundary: every entry point replaces one interface of
+ * the reference C++ library libsanm (citations are file:line into the
+ * reference checkout).  libsanm has no FFI of its own -- its seams are C++
+ * classes -- so the entry points are those classes flattened to C: opaque
+ * handles, plain pointers and sizes, `int` status returns (0 = ok; the message
+ * of the last failure on the calling thread is sanm_last_error()).
+ * INTEGRATION.md shows the reference-side binding (thin C++ classes with the
+ * libsanm names on top of this header).
+ *
+ * Conventions
+ *   - all numeric data is FP64; tensors are row-major with the batch first
+ *     (rank <= 3), shapes are passed as (rank, dims[rank]) with uint64 dims;
+ *   - `const double*` / `double*` arguments are HOST buffers unless the name
+ *     ends in `_dev`; host<->device copies happen inside the call;
+ *   - status codes mirror the reference's exception types
+ *     (libsanm/utils.h:19-50): 1 SANMError, 2 SANMAssertionError,
+ *     3 SANMNumericalError, 4 CUDA failure / no device (there is no CPU
+ *     fallback);
+ *   - one host thread drives a context; all kernels run on one CUDA stream.
+ */
+#ifndef SANM_B200_H
+#define SANM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SANM_OK 0
+#define SANM_ERR_GENERIC 1
+#define SANM_ERR_ASSERT 2
+#define SANM_ERR_NUMERICAL 3
+#define SANM_ERR_CUDA 4
+
+typedef struct sanm_graph sanm_graph_t;   /* ComputingGraph + its VarNodes  */
+typedef struct sanm_prop sanm_prop_t;     /* ParallelTaylorCoeffProp        */
+typedef struct sanm_remap sanm_remap_t;   /* SparseLinearDesc               */
+typedef struct sanm_sparse sanm_sparse_t; /* SparseSolver                   */
+typedef struct sanm_anm sanm_anm_t;       /* ANMSolverVecScale / ANMEqnSolver /
+                                             ANMImplicitSolver              */
+
+/* ---- library ------------------------------------------------------------ */
+const char* sanm_last_error(void);
+/* bind the calling process to a CUDA device (default: device 0) */
+int sanm_set_device(int device);
+/* kernels launched by this library since process start */
+uint64_t sanm_launch_count(void);
+/* block until every kernel queued by this library has finished */
+int sanm_synchronize(void);
+/* ScopedProfiler report (libsanm/utils.h:225-249): accumulated device time per
+ * tag, written as text into buf (truncated to cap bytes) */
+int sanm_prof_dump(char* buf, uint64_t cap);
+int sanm_prof_reset(void);
+/* accumulated milliseconds and call count of one tag; 0/0 if never seen */
+int sanm_prof_get(const char* tag, double* ms, uint64_t* calls);
+
+/* ---- symbolic graph: libsanm/symbolic.h:283-293, libsanm/oprs.h:14-105 ---- */
+/* variables are small integers local to their graph (a VarNode* identity) */
+int sanm_graph_create(sanm_graph_t** out);
+int sanm_graph_destroy(sanm_graph_t* g);
+/* symbolic::placeholder, oprs.h:80 */
+int sanm_graph_placeholder(sanm_graph_t* g, int* out_var);
+/* symbolic::constant, oprs.h:88; data is [batch, ...] */
+int sanm_graph_constant(sanm_graph_t* g, const double* data, int rank,
+                        const uint64_t* dims, int* out_var);
+/* symbolic::linear_combine, oprs.h:76: sum coeffs[i]*vars[i] + bias */
+int sanm_graph_linear_combine(sanm_graph_t* g, int n, const double* coeffs,
+                              const int* vars, double bias, int* out_var);
+/* SymbolVar::operator*(SymbolVar), oprs.h:30 */
+int sanm_graph_multiply(sanm_graph_t* g, int a, int b, int* out_var);
+/* SymbolVar::pow / log, oprs.h:55-58 */
+int sanm_graph_pow(sanm_graph_t* g, int x, double exponent, int* out_var);
+int sanm_graph_log(sanm_graph_t* g, int x, int* out_var);
+/* SymbolVar::reduce_sum, oprs.h:34 (axis -1 = all per-item elements) */
+int sanm_graph_reduce_sum(sanm_graph_t* g, int x, int axis, int keepdim,
+                          int* out_var);
+/* SymbolVar::batched_matmul / batched_transpose / batched_det /
+ * batched_mul_eye, oprs.h:37-52 */
+int sanm_graph_batched_matmul(sanm_graph_t* g, int a, int b, int* out_var);
+int sanm_graph_batched_transpose(sanm_graph_t* g, int x, int* out_var);
+int sanm_graph_batched_det(sanm_graph_t* g, int x, int* out_var);
+int sanm_graph_batched_mul_eye(sanm_graph_t* g, int x, uint64_t dim,
+                               int* out_var);
+/* symbolic::batched_mat_inv_mul, oprs.h:72: y with y@x = a (is_left) or
+ * x@y = a; a < 0 means the identity */
+int sanm_graph_batched_mat_inv_mul(sanm_graph_t* g, int x, int a, int is_left,
+                                   int* out_var);
+/* SymbolVar::batched_svd_w, oprs.h:61: out_vars = {U, S, W}, M = U S U^T W */
+int sanm_graph_batched_svd_w(sanm_graph_t* g, int x, int require_rotation,
+                             int* out_vars3);
+/* SymbolVar::slice, oprs.h:64 and symbolic::concat, oprs.h:104 */
+int sanm_graph_slice(sanm_graph_t* g, int x, int axis, int has_begin, int begin,
+                     int has_end, int end, int stride, int* out_var);
+int sanm_graph_concat(sanm_graph_t* g, int n, const int* vars, int axis,
+                      int* out_var);
+
+/* ---- Taylor propagation: ParallelTaylorCoeffProp, symbolic.h:391-423 ------ */
+/* max_order bounds the orders that will be requested (stacks are preallocated
+ * in HBM; the reference grows its arrays on demand) */
+int sanm_prop_create(sanm_graph_t* g, int out_var, int max_order,
+                     sanm_prop_t** out);
+int sanm_prop_destroy(sanm_prop_t* p);
+/* push_xi, symbolic.h:402; the first call is order 0 and fixes the shape */
+int sanm_prop_push_xi(sanm_prop_t* p, const double* x, int rank,
+                      const uint64_t* dims);
+/* shape of the output variable (valid after the first push_xi) */
+int sanm_prop_out_shape(sanm_prop_t* p, int* rank, uint64_t* dims);
+/* gather_yi, symbolic.h:414: output coefficient of the previous push_xi */
+int sanm_prop_gather_yi(sanm_prop_t* p, double* out);
+/* compute_next_order_bias, symbolic.h:405; out may be NULL */
+int sanm_prop_compute_next_order_bias(sanm_prop_t* p, double* out);
+/* get_jacobian, symbolic.h:411. type: 1 ELEMWISE coeff [batch, dim],
+ * 2 FULL coeff [batch, odim, idim] (tensor.h:509-516); out may be NULL to
+ * query the sizes only */
+int sanm_prop_get_jacobian(sanm_prop_t* p, int* type, uint64_t* batch,
+                           uint64_t* odim, uint64_t* idim, double* out);
+/* eval_unary_func, symbolic.h:426 */
+int sanm_eval_unary_func(sanm_graph_t* g, int out_var, const double* x,
+                         int rank, const uint64_t* dims, int* orank,
+                         uint64_t* odims, double* out);
+/* bytes of HBM held by the Taylor stacks of this propagator */
+int sanm_prop_arena_bytes(sanm_prop_t* p, uint64_t* out);
+
+/* ---- sparse linear maps: SparseLinearDesc, anm.h:24-85 -------------------- */
+/* CSR over flattened tensors: row i of the output reads
+ * idx[rowptr[i]..rowptr[i+1]) of the input with weights coeff[] -- what
+ * SparseLinearDesc::get(i) returns (anm.h:58) for every i */
+int sanm_remap_create(int out_rank, const uint64_t* out_dims, int in_rank,
+                      const uint64_t* in_dims, const uint64_t* rowptr,
+                      const uint64_t* idx, const double* coeff,
+                      sanm_remap_t** out);
+/* SparseLinearDesc::make_identity, anm.h:70 */
+int sanm_remap_identity(int in_rank, const uint64_t* in_dims, int out_rank,
+                        const uint64_t* out_dims, sanm_remap_t** out);
+int sanm_remap_destroy(sanm_remap_t* r);
+/* SparseLinearDesc::apply, anm.h:62 */
+int sanm_remap_apply(sanm_remap_t* r, const double* x, double* y);
+
+/* ---- sparse direct solver: SparseSolver, sparse_solver.h:17-87 ------------ */
+int sanm_sparse_create(uint64_t nr_unknowns, sanm_sparse_t** out);
+int sanm_sparse_destroy(sanm_sparse_t* s);
+/* SparseMatBuilder::add_constraint (sparse_solver.h:51) for a batch of COO
+ * entries; rows non-decreasing across calls, duplicates are summed, entries
+ * with |coeff| < 1e-9 are dropped (sparse_solver.cpp:291-293) */
+int sanm_sparse_add_constraints(sanm_sparse_t* s, uint64_t nnz,
+                                const uint64_t* cidx, const uint64_t* xidx,
+                                const double* coeff);
+/* prepare, sparse_solver.h:74: ordering + symbolic + numeric LU on the GPU;
+ * l2_penalty != 0 solves min |Ax-b|^2 + l2|x|^2 via (A'A + l2 I) x = A'b */
+int sanm_sparse_prepare(sanm_sparse_t* s, double l2_penalty);
+/* solve / apply / coeff_l2, sparse_solver.h:77-86 */
+int sanm_sparse_solve(sanm_sparse_t* s, const double* b, double* x);
+int sanm_sparse_apply(sanm_sparse_t* s, const double* x, double* y);
+int sanm_sparse_coeff_l2(sanm_sparse_t* s, double* out);
+/* factorization statistics: nnz(L)+nnz(U), flops of the numeric phase,
+ * number of supernodes, number of levels of the elimination forest */
+int sanm_sparse_stats(sanm_sparse_t* s, uint64_t* nnz_lu, double* flops,
+                      uint64_t* nr_supernodes, uint64_t* nr_levels);
+
+/* ---- ANM drivers: anm.h:98-305 -------------------------------------------- */
+/* ANMDriverHelper::HyperParam (anm.h:100-114) + ANMEqnSolver::HyperParam
+ * (anm.h:244-248) */
+typedef struct sanm_anm_hyper {
+    int use_pade;
+    int sanity_check;
+    int order;
+    double maxr;
+    double solution_check_tol;
+    double xcoeff_l2_penalty;
+    double converge_rms;
+} sanm_anm_hyper_t;
+/* fills the reference's defaults (order 8, maxr 1e-6, tol 1e-4, ...) */
+void sanm_anm_hyper_default(sanm_anm_hyper_t* h);
+
+/* ANMSolverVecScale, anm.h:213: f(x) + t*v = 0 */
+int sanm_anm_vecscale_create(sanm_graph_t* g, int f, sanm_remap_t* remap_inp,
+                             sanm_remap_t* remap_out, const double* x0,
+                             int x_rank, const uint64_t* x_dims, double t0,
+                             const double* v, int v_rank,
+                             const uint64_t* v_dims,
+                             const sanm_anm_hyper_t* hyper, sanm_anm_t** out);
+/* ANMEqnSolver, anm.h:242: f(x) + y = 0 */
+int sanm_anm_eqn_create(sanm_graph_t* g, int f, sanm_remap_t* remap_inp,
+                        sanm_remap_t* remap_out, const double* x0, int x_rank,
+                        const uint64_t* x_dims, const double* y, int y_rank,
+                        const uint64_t* y_dims, const sanm_anm_hyper_t* hyper,
+                        sanm_anm_t** out);
+/* ANMImplicitSolver, anm.h:277: F(x, t) = F(x0, t0) */
+int sanm_anm_implicit_create(sanm_graph_t* g, int f, sanm_remap_t* remap_inp,
+                             sanm_remap_t* remap_out, const double* x0,
+                             uint64_t n, double t0,
+                             const sanm_anm_hyper_t* hyper, sanm_anm_t** out);
+int sanm_anm_destroy(sanm_anm_t* a);
+/* ANMDriverHelper::update_approx / get_t_upper / solve_a / eval / xt_coeffs /
+ * get_nr_ieter, anm.h:116-139 (vecscale and implicit solvers) */
+int sanm_anm_update_approx(sanm_anm_t* a);
+int sanm_anm_get_t_upper(sanm_anm_t* a, double* out);
+int sanm_anm_solve_a(sanm_anm_t* a, double t, double* out);
+int sanm_anm_eval(sanm_anm_t* a, double aval, double* x_out, double* t_out);
+int sanm_anm_nr_iter(sanm_anm_t* a, uint64_t* out);
+int sanm_anm_nr_xt_coeffs(sanm_anm_t* a, uint64_t* out);
+int sanm_anm_xt_coeff(sanm_anm_t* a, uint64_t i, double* out);
+/* ANMEqnSolver::next_iter / converged / residual_rms / get_x, anm.h:253-263 */
+int sanm_anm_eqn_next_iter(sanm_anm_t* a);
+int sanm_anm_eqn_converged(sanm_anm_t* a, int* out);
+int sanm_anm_eqn_residual_rms(sanm_anm_t* a, double* out);
+int sanm_anm_eqn_get_x(sanm_anm_t* a, double* out);
+/* ANMImplicitSolver::fx0, anm.h:285 */
+int sanm_anm_implicit_fx0(sanm_anm_t* a, double* out);
+/* counters of the element phase of this solver: tet*order steps propagated
+ * and the device milliseconds spent in gather + propagation + assembly
+ * kernels (CUDA events on the library stream) */
+int sanm_anm_element_stats(sanm_anm_t* a, double* tet_order_steps,
+                           double* element_ms, double* solve_ms,
+                           double* factor_ms, double* assemble_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SANM_B200_H */

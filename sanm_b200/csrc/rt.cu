@@ -1,0 +1,109 @@
+/* sanm_b200/csrc/rt.cu -- runtime layer implementation (see rt.h). */
+#include "rt.h"
+
+#include <atomic>
+
+namespace sanm_b200 {
+namespace rt {
+
+namespace {
+std::atomic<uint64_t> g_launches{0};
+}
+
+uint64_t launch_count() { return g_launches.load(); }
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+#ifdef SANM_HOSTEMU
+
+stream_t stream() { return 0; }
+void sync() {}
+void* dmalloc(size_t bytes) {
+    void* p = malloc(bytes ? bytes : 1);
+    if (!p) sanm_throw(SANM_ERR_GENERIC, "host-emulation malloc(%zu) failed", bytes);
+    return p;
+}
+void dfree(void* p) { free(p); }
+void h2d(void* dst, const void* src, size_t bytes) { memcpy(dst, src, bytes); }
+void d2h(void* dst, const void* src, size_t bytes) { memcpy(dst, src, bytes); }
+void d2d(void* dst, const void* src, size_t bytes) { memmove(dst, src, bytes); }
+void dzero(void* dst, size_t bytes) { memset(dst, 0, bytes); }
+void* hmalloc_pinned(size_t bytes) { return malloc(bytes ? bytes : 1); }
+void hfree_pinned(void* p) { free(p); }
+
+#else
+
+namespace {
+cudaStream_t g_stream = nullptr;
+bool g_device_ok = false;
+}  // namespace
+
+void check_device() {
+    if (g_device_ok) return;
+    int n = 0;
+    cudaError_t err = cudaGetDeviceCount(&n);
+    if (err != cudaSuccess || n <= 0) {
+        // no CPU fallback: the product path needs a CUDA device
+        throw Error{SANM_ERR_CUDA,
+                    std::string{"sanm_b200 requires a CUDA device (sm_100a): "} +
+                            (err != cudaSuccess ? cudaGetErrorString(err)
+                                                : "no device found")};
+    }
+    SANM_CUDA_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+    g_device_ok = true;
+}
+
+stream_t stream() {
+    check_device();
+    return g_stream;
+}
+
+void sync() { SANM_CUDA_CHECK(cudaStreamSynchronize(stream())); }
+
+void* dmalloc(size_t bytes) {
+    check_device();
+    void* p = nullptr;
+    SANM_CUDA_CHECK(cudaMalloc(&p, bytes ? bytes : 1));
+    return p;
+}
+
+void dfree(void* p) {
+    if (p) cudaFree(p);
+}
+
+void h2d(void* dst, const void* src, size_t bytes) {
+    SANM_CUDA_CHECK(
+            cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream()));
+    // the source may be pageable / reused by the caller right away
+    SANM_CUDA_CHECK(cudaStreamSynchronize(stream()));
+}
+
+void d2h(void* dst, const void* src, size_t bytes) {
+    SANM_CUDA_CHECK(
+            cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream()));
+    SANM_CUDA_CHECK(cudaStreamSynchronize(stream()));
+}
+
+void d2d(void* dst, const void* src, size_t bytes) {
+    SANM_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice,
+                                    stream()));
+}
+
+void dzero(void* dst, size_t bytes) {
+    SANM_CUDA_CHECK(cudaMemsetAsync(dst, 0, bytes, stream()));
+}
+
+void* hmalloc_pinned(size_t bytes) {
+    check_device();
+    void* p = nullptr;
+    SANM_CUDA_CHECK(cudaMallocHost(&p, bytes ? bytes : 1));
+    return p;
+}
+
+void hfree_pinned(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+#endif
+
+}  // namespace rt
+}  // namespace sanm_b200

@@ -1,0 +1,246 @@
+/* sanm_b200/csrc/rt.h -- thin runtime layer under every kernel in this library.
+ *
+ * Product build (nvcc, sm_100a): device memory, one CUDA stream, kernels.
+ * SANM_HOSTEMU build (g++ -x c++): the SAME kernel bodies run as plain loops
+ * on the host.  That build exists only so that the CPU-only development
+ * container can check kernel *logic* against the oracle (tests/, `-m "not gpu"`);
+ * it is compiled by tests/hostemu_build.py into tests/_hostemu/ and is never
+ * loaded by the sanm_b200 package -- the product library has no CPU fallback
+ * and every entry point fails with SANM_ERR_CUDA when no device is present.
+ *
+ * Kernel-writing discipline that makes the dual build possible:
+ *   - per-item kernels are functors run through rt::for_each (one thread per
+ *     item, item index fastest-varying in every array => coalesced);
+ *   - block-cooperative kernels are functors run through rt::for_each_block;
+ *     inside, work is written as `for (i = tid; i < n; i += nthr)` phases
+ *     separated by ctx.sync(); threads communicate only through shared memory
+ *     across a sync().  In the host build nthr == 1 and sync() is a no-op.
+ */
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/sanm_b200.h"
+
+#ifdef SANM_HOSTEMU
+#define SANM_HD
+#define SANM_D
+#include <cmath>
+#else
+#include <cuda_runtime.h>
+#define SANM_HD __host__ __device__
+#define SANM_D __device__
+#endif
+
+namespace sanm_b200 {
+
+// status codes (SANM_OK, SANM_ERR_*) come from the public header
+
+struct Error : public std::runtime_error {
+    int code;
+    Error(int c, const std::string& msg) : std::runtime_error{msg}, code{c} {}
+};
+
+std::string ssprintf(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+
+#define sanm_throw(code, ...) \
+    throw ::sanm_b200::Error { code, ::sanm_b200::ssprintf(__VA_ARGS__) }
+
+#define sanm_check(expr, ...)                                               \
+    do {                                                                    \
+        if (!(expr)) {                                                      \
+            throw ::sanm_b200::Error{                                       \
+                    SANM_ERR_ASSERT,                           \
+                    std::string{"assertion `" #expr "' failed at "} +       \
+                            __FILE__ + ":" + std::to_string(__LINE__) +     \
+                            ": " + ::sanm_b200::ssprintf("" __VA_ARGS__)};  \
+        }                                                                   \
+    } while (0)
+
+namespace rt {
+
+#ifdef SANM_HOSTEMU
+using stream_t = int;
+inline void check_device() {}
+#define SANM_CUDA_CHECK(x) (void)(x)
+#else
+using stream_t = cudaStream_t;
+#define SANM_CUDA_CHECK(x)                                                  \
+    do {                                                                    \
+        cudaError_t err__ = (x);                                            \
+        if (err__ != cudaSuccess) {                                         \
+            throw ::sanm_b200::Error{                                       \
+                    SANM_ERR_CUDA,                             \
+                    std::string{"CUDA error at "} + __FILE__ + ":" +        \
+                            std::to_string(__LINE__) + ": " +               \
+                            cudaGetErrorString(err__)};                     \
+        }                                                                   \
+    } while (0)
+void check_device();
+#endif
+
+//! the single stream every kernel of this library is launched on
+stream_t stream();
+void sync();
+
+void* dmalloc(size_t bytes);
+void dfree(void* p);
+void h2d(void* dst, const void* src, size_t bytes);
+void d2h(void* dst, const void* src, size_t bytes);
+void d2d(void* dst, const void* src, size_t bytes);
+void dzero(void* dst, size_t bytes);
+//! pinned host staging memory (plain malloc in the host build)
+void* hmalloc_pinned(size_t bytes);
+void hfree_pinned(void* p);
+
+//! number of kernels launched by this library since process start
+uint64_t launch_count();
+void count_launch();
+
+//! owning device buffer
+template <typename T>
+class DBuf {
+    T* m_p = nullptr;
+    size_t m_n = 0;
+
+public:
+    DBuf() = default;
+    explicit DBuf(size_t n) { alloc(n); }
+    DBuf(const DBuf&) = delete;
+    DBuf& operator=(const DBuf&) = delete;
+    DBuf(DBuf&& o) noexcept : m_p{o.m_p}, m_n{o.m_n} {
+        o.m_p = nullptr;
+        o.m_n = 0;
+    }
+    DBuf& operator=(DBuf&& o) noexcept {
+        if (this != &o) {
+            release();
+            m_p = o.m_p;
+            m_n = o.m_n;
+            o.m_p = nullptr;
+            o.m_n = 0;
+        }
+        return *this;
+    }
+    ~DBuf() { release(); }
+    void release() {
+        if (m_p) dfree(m_p);
+        m_p = nullptr;
+        m_n = 0;
+    }
+    void alloc(size_t n) {
+        release();
+        if (n) m_p = static_cast<T*>(dmalloc(n * sizeof(T)));
+        m_n = n;
+    }
+    //! grow-only allocation; contents are NOT preserved
+    void ensure(size_t n) {
+        if (n > m_n) alloc(n);
+    }
+    void upload(const T* src, size_t n) {
+        ensure(n);
+        if (n) h2d(m_p, src, n * sizeof(T));
+    }
+    void upload(const std::vector<T>& v) { upload(v.data(), v.size()); }
+    void download(T* dst, size_t n) const {
+        if (n) d2h(dst, m_p, n * sizeof(T));
+    }
+    std::vector<T> to_host() const {
+        std::vector<T> v(m_n);
+        download(v.data(), m_n);
+        return v;
+    }
+    void zero() {
+        if (m_n) dzero(m_p, m_n * sizeof(T));
+    }
+    T* ptr() const { return m_p; }
+    size_t size() const { return m_n; }
+};
+
+#ifdef SANM_HOSTEMU
+/* ---------------------------------------------------------------- host */
+template <class F>
+void for_each(size_t n, const F& f) {
+    count_launch();
+    for (size_t i = 0; i < n; ++i) f(i);
+}
+
+struct BlockCtx {
+    int tid = 0, nthr = 1;
+    size_t bid = 0;
+    char* smem = nullptr;
+    void sync() const {}
+};
+
+template <class F>
+void for_each_block(size_t nblocks, int /*threads*/, size_t smem_bytes,
+                    const F& f) {
+    count_launch();
+    std::vector<char> sm(smem_bytes + 16);
+    for (size_t b = 0; b < nblocks; ++b) {
+        BlockCtx c;
+        c.bid = b;
+        c.smem = sm.data();
+        f(c);
+    }
+}
+#else
+/* ---------------------------------------------------------------- CUDA */
+template <class F>
+__global__ void k_for_each(F f, size_t n) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) f(i);
+}
+
+template <class F, int THREADS = 128>
+void for_each(size_t n, const F& f) {
+    if (!n) return;
+    count_launch();
+    size_t blocks = (n + THREADS - 1) / THREADS;
+    k_for_each<F><<<(unsigned)blocks, THREADS, 0, stream()>>>(f, n);
+    SANM_CUDA_CHECK(cudaGetLastError());
+}
+
+struct BlockCtx {
+    int tid, nthr;
+    size_t bid;
+    char* smem;
+    __device__ void sync() const { __syncthreads(); }
+};
+
+template <class F>
+__global__ void k_for_each_block(F f) {
+    extern __shared__ __align__(16) char smem_raw[];
+    BlockCtx c;
+    c.tid = threadIdx.x;
+    c.nthr = blockDim.x;
+    c.bid = blockIdx.x;
+    c.smem = smem_raw;
+    f(c);
+}
+
+template <class F>
+void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
+                    const F& f) {
+    if (!nblocks) return;
+    count_launch();
+    if (smem_bytes > 48 * 1024) {
+        SANM_CUDA_CHECK(cudaFuncSetAttribute(
+                k_for_each_block<F>,
+                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    }
+    k_for_each_block<F>
+            <<<(unsigned)nblocks, threads, smem_bytes, stream()>>>(f);
+    SANM_CUDA_CHECK(cudaGetLastError());
+}
+#endif
+
+}  // namespace rt
+}  // namespace sanm_b200
