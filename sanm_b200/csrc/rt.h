@@ -64,6 +64,14 @@ std::string ssprintf(const char* fmt, ...) __attribute__((format(printf, 1, 2)))
         }                                                                   \
     } while (0)
 
+SANM_HD inline void rt_atomic_inc(int* p) {
+#if defined(__CUDA_ARCH__)
+    atomicAdd(p, 1);
+#else
+    ++*p;
+#endif
+}
+
 namespace rt {
 
 #ifdef SANM_HOSTEMU

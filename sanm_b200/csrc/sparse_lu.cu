@@ -1,0 +1,670 @@
+/* sanm_b200/csrc/sparse_lu.cu -- numeric multifrontal factorisation and solves
+ * (see sparse_lu.h for the algorithm). */
+#include "sparse_lu.h"
+#include "sparse_symbolic.h"
+
+#include <algorithm>
+#include <cmath>
+
+namespace sanm_b200 {
+
+namespace {
+
+constexpr int NB = 32;          //!< pivot block of the large-front path
+constexpr uint32_t SMALL_NR = 104;  //!< fronts up to this size live in smem
+constexpr int ASM_TILE = 4096;  //!< entries per assembly task
+constexpr int ROW_CHUNK = 256;  //!< rows per solve task
+
+struct FrontD {
+    double* F;        //!< nr x nr, column-major
+    double* vec;      //!< solve workspace [nr]: [w1' ; update]
+    const uint32_t* st;  //!< row structure (permuted indices)
+    const int32_t* inv;  //!< map parent row -> own update row (size nr_parent)
+    uint32_t* rowperm;   //!< [nc] row permutation of the pivot block
+    uint32_t nr, nc, c0;
+    uint32_t child_begin, child_end;
+    int32_t parent;
+};
+
+struct Task {
+    uint32_t front, chunk;
+};
+
+/* ---------------------------------------------------------------- kernels */
+
+struct ScatterA {
+    double* fronts;
+    const uint64_t* dest;
+    const double* vals;
+    SANM_D void operator()(size_t p) const { fronts[dest[p]] = vals[p]; }
+};
+
+struct AbsMaxKernel {
+    const double* v;
+    uint64_t n;
+    double* out;  // out[0] = max |v|
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        double* red = reinterpret_cast<double*>(c.smem);
+        double m = 0;
+        for (uint64_t i = c.tid; i < n; i += c.nthr) {
+            double a = fabs(v[i]);
+            m = a > m ? a : m;
+        }
+        red[c.tid] = m;
+        c.sync();
+        for (int s = c.nthr / 2; s > 0; s >>= 1) {
+            if (c.tid < s) red[c.tid] = red[c.tid] > red[c.tid + s] ? red[c.tid] : red[c.tid + s];
+            c.sync();
+        }
+        if (c.tid == 0) out[0] = red[0];
+    }
+};
+
+//! F[i,j] += sum over children of their Schur complement entry (gather form)
+struct AssembleChildren {
+    const FrontD* fronts;
+    const uint32_t* child_list;
+    const Task* tasks;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const Task tk = tasks[c.bid];
+        const FrontD f = fronts[tk.front];
+        const uint64_t total = (uint64_t)f.nr * f.nr;
+        const uint64_t e0 = (uint64_t)tk.chunk * ASM_TILE;
+        const uint64_t e1 = e0 + ASM_TILE < total ? e0 + ASM_TILE : total;
+        for (uint64_t e = e0 + c.tid; e < e1; e += c.nthr) {
+            const uint32_t i = (uint32_t)(e % f.nr), j = (uint32_t)(e / f.nr);
+            double acc = 0;
+            for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
+                const FrontD ch = fronts[child_list[q]];
+                const int32_t ii = ch.inv[i], jj = ch.inv[j];
+                if (ii >= 0 && jj >= 0) {
+                    acc += ch.F[(uint64_t)(ch.nc + jj) * ch.nr + ch.nc + ii];
+                }
+            }
+            f.F[e] += acc;
+        }
+    }
+};
+
+/*!
+ * In-place Gauss-Jordan on the first nb pivots starting at k0 of an m x m
+ * column-major matrix M (leading dim ld), pivoting among rows [k, plim).
+ * Runs inside one CTA; `sh` is one shared int used to broadcast the pivot row.
+ */
+SANM_D inline void gj_steps(const rt::BlockCtx& c, double* M, uint32_t ld,
+                            uint32_t m, uint32_t k0, uint32_t nb, uint32_t plim,
+                            uint32_t* rowperm, int* sh, double thresh,
+                            int* nr_perturbed) {
+    for (uint32_t k = k0; k < k0 + nb; ++k) {
+        if (c.tid == 0) {
+            uint32_t r = k;
+            double best = fabs(M[(uint64_t)k * ld + k]);
+            for (uint32_t i = k + 1; i < plim; ++i) {
+                double a = fabs(M[(uint64_t)k * ld + i]);
+                if (a > best) {
+                    best = a;
+                    r = i;
+                }
+            }
+            if (!(best > thresh)) {
+                // static pivot perturbation (as PARDISO does for tiny pivots)
+                double p = M[(uint64_t)k * ld + r];
+                M[(uint64_t)k * ld + r] = p < 0 ? -thresh : thresh;
+                rt_atomic_inc(nr_perturbed);
+            }
+            *sh = (int)r;
+        }
+        c.sync();
+        const uint32_t r = (uint32_t)*sh;
+        if (r != k) {
+            for (uint32_t j = c.tid; j < m; j += c.nthr) {
+                double a = M[(uint64_t)j * ld + k];
+                M[(uint64_t)j * ld + k] = M[(uint64_t)j * ld + r];
+                M[(uint64_t)j * ld + r] = a;
+            }
+            if (c.tid == 0 && rowperm) {
+                uint32_t a = rowperm[k];
+                rowperm[k] = rowperm[r];
+                rowperm[r] = a;
+            }
+        }
+        c.sync();
+        const double ip = 1.0 / M[(uint64_t)k * ld + k];
+        for (uint32_t j = c.tid; j < m; j += c.nthr) {
+            if (j != k) M[(uint64_t)j * ld + k] *= ip;
+        }
+        c.sync();
+        const uint64_t tot = (uint64_t)m * m;
+        for (uint64_t e = c.tid; e < tot; e += c.nthr) {
+            const uint32_t i = (uint32_t)(e % m), j = (uint32_t)(e / m);
+            if (i != k && j != k) {
+                M[(uint64_t)j * ld + i] -= M[(uint64_t)k * ld + i] * M[(uint64_t)j * ld + k];
+            }
+        }
+        c.sync();
+        for (uint32_t i = c.tid; i < m; i += c.nthr) {
+            double* p = M + (uint64_t)k * ld + i;
+            *p = i == k ? ip : -(*p) * ip;
+        }
+        c.sync();
+    }
+}
+
+//! whole small front in shared memory, one CTA per front
+struct SmallFrontKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    const double* amax;
+    int* nr_perturbed;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const FrontD f = fronts[list[c.bid]];
+        double* M = reinterpret_cast<double*>(c.smem);
+        int* sh = reinterpret_cast<int*>(M + (uint64_t)f.nr * f.nr);
+        const uint64_t tot = (uint64_t)f.nr * f.nr;
+        for (uint64_t e = c.tid; e < tot; e += c.nthr) M[e] = f.F[e];
+        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) f.rowperm[i] = i;
+        c.sync();
+        gj_steps(c, M, f.nr, f.nr, 0, f.nc, f.nc, f.rowperm, sh,
+                 amax[0] * 1e-13, nr_perturbed);
+        for (uint64_t e = c.tid; e < tot; e += c.nthr) f.F[e] = M[e];
+    }
+};
+
+/* ---- large fronts: blocked Gauss-Jordan in global memory, NB pivots a step */
+
+//! invert the diagonal block (with pivoting inside it) and apply its row
+//! swaps to the rest of the block row
+struct BigDiagKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb;
+    const double* amax;
+    int* nr_perturbed;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const FrontD f = fronts[list[c.bid]];
+        if (kb >= f.nc) return;
+        const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
+        double* D = reinterpret_cast<double*>(c.smem);  // nb x nb, ld NB
+        uint32_t* lperm = reinterpret_cast<uint32_t*>(D + NB * NB);
+        int* sh = reinterpret_cast<int*>(lperm + NB);
+        if (kb == 0) {
+            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) f.rowperm[i] = i;
+        }
+        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            D[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
+        }
+        for (uint32_t i = c.tid; i < nb; i += c.nthr) lperm[i] = i;
+        c.sync();
+        gj_steps(c, D, NB, nb, 0, nb, nb, lperm, sh, amax[0] * 1e-13,
+                 nr_perturbed);
+        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            f.F[(uint64_t)(kb + j) * f.nr + kb + i] = D[j * NB + i];
+        }
+        // row i of the block now holds original row lperm[i]: permute the rest
+        // of the block row accordingly (columns outside the diagonal block)
+        for (uint32_t j = c.tid; j < f.nr; j += c.nthr) {
+            if (j >= kb && j < kb + nb) continue;
+            double* col = f.F + (uint64_t)j * f.nr + kb;
+            double tmp[NB];
+            for (uint32_t i = 0; i < nb; ++i) tmp[i] = col[lperm[i]];
+            for (uint32_t i = 0; i < nb; ++i) col[i] = tmp[i];
+        }
+        c.sync();
+        if (c.tid == 0) {
+            uint32_t tmp[NB];
+            for (uint32_t i = 0; i < nb; ++i) tmp[i] = f.rowperm[kb + lperm[i]];
+            for (uint32_t i = 0; i < nb; ++i) f.rowperm[kb + i] = tmp[i];
+        }
+    }
+};
+
+//! R' = Dinv * R for a tile of 64 columns outside the pivot block
+struct BigRowPanelKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb, tiles;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const FrontD f = fronts[list[c.bid / tiles]];
+        const uint32_t tile = (uint32_t)(c.bid % tiles);
+        if (kb >= f.nc || tile * 64 >= f.nr) return;
+        const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
+        double* Di = reinterpret_cast<double*>(c.smem);  // [NB*NB]
+        double* R = Di + NB * NB;                        // [NB*64]
+        const uint32_t j0 = tile * 64;
+        const uint32_t nj = f.nr - j0 < 64 ? f.nr - j0 : 64;
+        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
+        }
+        for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + i];
+        }
+        c.sync();
+        for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            uint32_t gj = j0 + j;
+            if (gj >= kb && gj < kb + nb) continue;
+            double s = 0;
+            for (uint32_t m = 0; m < nb; ++m) s += Di[m * NB + i] * R[j * NB + m];
+            f.F[(uint64_t)gj * f.nr + kb + i] = s;
+        }
+    }
+};
+
+//! T -= C * R' on a 64x64 tile (rows and columns of the pivot block excluded)
+struct BigGemmKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb, tiles;  // tiles per dimension
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const uint32_t per = tiles * tiles;
+        const FrontD f = fronts[list[c.bid / per]];
+        const uint32_t t = (uint32_t)(c.bid % per), ti = t % tiles, tj = t / tiles;
+        if (kb >= f.nc || ti * 64 >= f.nr || tj * 64 >= f.nr) return;
+        const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
+        double* Cs = reinterpret_cast<double*>(c.smem);  // [NB][64] : Cs[m*64+i]
+        double* Rs = Cs + NB * 64;                       // [64][NB] : Rs[j*NB+m]
+        const uint32_t i0 = ti * 64, j0 = tj * 64;
+        const uint32_t ni = f.nr - i0 < 64 ? f.nr - i0 : 64;
+        const uint32_t nj = f.nr - j0 < 64 ? f.nr - j0 : 64;
+        for (uint32_t e = c.tid; e < nb * 64; e += c.nthr) {
+            uint32_t i = e % 64, m = e / 64;
+            Cs[m * 64 + i] = i < ni ? f.F[(uint64_t)(kb + m) * f.nr + i0 + i] : 0.0;
+        }
+        for (uint32_t e = c.tid; e < nb * 64; e += c.nthr) {
+            uint32_t m = e % nb, j = e / nb;
+            Rs[j * NB + m] = j < nj ? f.F[(uint64_t)(j0 + j) * f.nr + kb + m] : 0.0;
+        }
+        c.sync();
+        // 16 x 16 thread grid in the CUDA build (256 threads), 4x4 per thread;
+        // generic strided form so that the host build (1 thread) is the same code
+        for (uint32_t q = c.tid; q < 256; q += c.nthr) {
+            const uint32_t qi = (q % 16) * 4, qj = (q / 16) * 4;
+            double acc[4][4] = {};
+            for (uint32_t m = 0; m < nb; ++m) {
+                double a[4], b[4];
+                for (int u = 0; u < 4; ++u) a[u] = Cs[m * 64 + qi + u];
+                for (int u = 0; u < 4; ++u) b[u] = Rs[(qj + u) * NB + m];
+                for (int u = 0; u < 4; ++u)
+                    for (int v = 0; v < 4; ++v) acc[u][v] += a[u] * b[v];
+            }
+            for (int v = 0; v < 4; ++v) {
+                const uint32_t gj = j0 + qj + v;
+                if (qj + v >= nj || (gj >= kb && gj < kb + nb)) continue;
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t gi = i0 + qi + u;
+                    if (qi + u >= ni || (gi >= kb && gi < kb + nb)) continue;
+                    f.F[(uint64_t)gj * f.nr + gi] -= acc[u][v];
+                }
+            }
+        }
+    }
+};
+
+//! C' = -C * Dinv for a tile of 64 rows outside the pivot block
+struct BigColPanelKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb, tiles;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const FrontD f = fronts[list[c.bid / tiles]];
+        const uint32_t tile = (uint32_t)(c.bid % tiles);
+        if (kb >= f.nc || tile * 64 >= f.nr) return;
+        const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
+        double* Di = reinterpret_cast<double*>(c.smem);  // [NB*NB]
+        double* Cs = Di + NB * NB;                       // [NB][64]
+        const uint32_t i0 = tile * 64;
+        const uint32_t ni = f.nr - i0 < 64 ? f.nr - i0 : 64;
+        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
+        }
+        for (uint32_t e = c.tid; e < nb * ni; e += c.nthr) {
+            uint32_t i = e % ni, m = e / ni;
+            Cs[m * 64 + i] = f.F[(uint64_t)(kb + m) * f.nr + i0 + i];
+        }
+        c.sync();
+        for (uint32_t e = c.tid; e < nb * ni; e += c.nthr) {
+            uint32_t i = e % ni, q = e / ni;
+            uint32_t gi = i0 + i;
+            if (gi >= kb && gi < kb + nb) continue;
+            double s = 0;
+            for (uint32_t m = 0; m < nb; ++m) s += Cs[m * 64 + i] * Di[q * NB + m];
+            f.F[(uint64_t)(kb + q) * f.nr + gi] = -s;
+        }
+    }
+};
+
+/* ---- solves */
+
+struct PermuteIn {
+    double* dst;
+    const double* src;
+    const uint32_t* perm;
+    SANM_D void operator()(size_t i) const { dst[i] = src[perm[i]]; }
+};
+struct PermuteOut {
+    double* dst;
+    const double* src;
+    const uint32_t* perm;
+    SANM_D void operator()(size_t i) const { dst[perm[i]] = src[i]; }
+};
+
+//! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates
+struct ForwardKernel {
+    const FrontD* fronts;
+    const uint32_t* child_list;
+    const Task* tasks;
+    const double* bp;  // permuted right-hand side
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const Task tk = tasks[c.bid];
+        const FrontD f = fronts[tk.front];
+        double* w1 = reinterpret_cast<double*>(c.smem);
+        double* w1p = w1 + f.nc;
+        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
+            double v = bp[f.c0 + i];
+            for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
+                const FrontD ch = fronts[child_list[q]];
+                const int32_t ii = ch.inv[i];
+                if (ii >= 0) v += ch.vec[ch.nc + ii];
+            }
+            w1[i] = v;
+        }
+        c.sync();
+        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
+            w1p[i] = w1[f.rowperm[i]];
+            if (tk.chunk == 0) f.vec[i] = w1p[i];
+        }
+        c.sync();
+        const uint32_t nu = f.nr - f.nc;
+        const uint32_t r0 = tk.chunk * ROW_CHUNK;
+        const uint32_t r1 = r0 + ROW_CHUNK < nu ? r0 + ROW_CHUNK : nu;
+        for (uint32_t i = r0 + c.tid; i < r1; i += c.nthr) {
+            double acc = 0;
+            for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
+                const FrontD ch = fronts[child_list[q]];
+                const int32_t ii = ch.inv[f.nc + i];
+                if (ii >= 0) acc += ch.vec[ch.nc + ii];
+            }
+            const double* row = f.F + f.nc + i;
+            for (uint32_t j = 0; j < f.nc; ++j) {
+                acc += row[(uint64_t)j * f.nr] * w1p[j];
+            }
+            f.vec[f.nc + i] = acc;
+        }
+    }
+};
+
+//! backward: x1 = G w1' - F12' x2
+struct BackwardKernel {
+    const FrontD* fronts;
+    const Task* tasks;
+    double* xp;  // permuted solution
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        const Task tk = tasks[c.bid];
+        const FrontD f = fronts[tk.front];
+        double* w1p = reinterpret_cast<double*>(c.smem);
+        double* x2 = w1p + f.nc;
+        const uint32_t nu = f.nr - f.nc;
+        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) w1p[i] = f.vec[i];
+        for (uint32_t i = c.tid; i < nu; i += c.nthr) x2[i] = xp[f.st[f.nc + i]];
+        c.sync();
+        const uint32_t r0 = tk.chunk * ROW_CHUNK;
+        const uint32_t r1 = r0 + ROW_CHUNK < f.nc ? r0 + ROW_CHUNK : f.nc;
+        for (uint32_t i = r0 + c.tid; i < r1; i += c.nthr) {
+            const double* row = f.F + i;
+            double acc = 0;
+            for (uint32_t j = 0; j < f.nc; ++j) acc += row[(uint64_t)j * f.nr] * w1p[j];
+            const double* row2 = row + (uint64_t)f.nc * f.nr;
+            for (uint32_t j = 0; j < nu; ++j) acc -= row2[(uint64_t)j * f.nr] * x2[j];
+            xp[f.c0 + i] = acc;
+        }
+    }
+};
+
+struct SpmvKernel {
+    const uint32_t* rowptr;
+    const uint32_t* colidx;
+    const double* vals;
+    const double* x;
+    double* y;
+    SANM_D void operator()(size_t i) const {
+        double s = 0;
+        for (uint32_t p = rowptr[i]; p < rowptr[i + 1]; ++p) s += vals[p] * x[colidx[p]];
+        y[i] = s;
+    }
+};
+
+}  // namespace
+
+struct SparseLU::Impl {
+    Symbolic sym;
+    std::vector<uint32_t> h_rowptr, h_colidx;
+    rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list, rowperm;
+    rt::DBuf<int32_t> inv;
+    rt::DBuf<uint64_t> a_dest;
+    rt::DBuf<double> fronts, vecs, vals, bp, xp, scal;
+    rt::DBuf<int> counters;
+    rt::DBuf<FrontD> fd;
+    // per-level launch lists
+    struct Level {
+        uint32_t asm_off = 0, asm_n = 0;      //!< assembly tasks
+        uint32_t small_off = 0, small_n = 0;  //!< list of small fronts
+        uint32_t big_off = 0, big_n = 0;      //!< list of large fronts
+        uint32_t big_max_nc = 0, big_max_nr = 0, small_max_nr = 0;
+        uint32_t fwd_off = 0, fwd_n = 0, bwd_off = 0, bwd_n = 0;
+        uint32_t max_nc = 0, max_nr = 0;
+    };
+    std::vector<Level> levels;
+    rt::DBuf<Task> asm_tasks, fwd_tasks, bwd_tasks;
+    rt::DBuf<uint32_t> small_list, big_list;
+    bool factored = false;
+};
+
+SparseLU::SparseLU() : m_impl{new Impl} {}
+SparseLU::~SparseLU() = default;
+
+const uint32_t* SparseLU::d_rowptr() const { return m_impl->rowptr.ptr(); }
+const uint32_t* SparseLU::d_colidx() const { return m_impl->colidx.ptr(); }
+
+void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
+                       const uint32_t* colidx) {
+    rt::check_device();
+    sanm_check(n > 0 && n < (1ull << 31));
+    Impl& I = *m_impl;
+    m_n = n;
+    m_nnz = rowptr[n];
+    I.h_rowptr.assign(rowptr, rowptr + n + 1);
+    I.h_colidx.assign(colidx, colidx + m_nnz);
+    I.sym = symbolic_analyze((uint32_t)n, rowptr, colidx);
+    const Symbolic& S = I.sym;
+
+    I.rowptr.upload(I.h_rowptr);
+    I.colidx.upload(I.h_colidx);
+    I.perm.upload(S.perm);
+    I.structs.upload(S.structs);
+    I.child_list.upload(S.child_list);
+    I.inv.upload(S.inv);
+    I.a_dest.upload(S.a_dest);
+    I.fronts.alloc(S.front_total);
+    I.vecs.alloc(S.soff[S.nsn]);
+    I.rowperm.alloc(n);
+    I.vals.alloc(m_nnz);
+    I.bp.alloc(n);
+    I.xp.alloc(n);
+    I.scal.alloc(4);
+    I.counters.alloc(4);
+    I.counters.zero();
+
+    std::vector<FrontD> fd(S.nsn);
+    uint32_t max_front = 0;
+    for (uint32_t s = 0; s < S.nsn; ++s) {
+        FrontD& f = fd[s];
+        f.F = I.fronts.ptr() + S.foff[s];
+        f.vec = I.vecs.ptr() + S.soff[s];
+        f.st = I.structs.ptr() + S.soff[s];
+        f.inv = S.sn_parent[s] >= 0 ? I.inv.ptr() + S.inv_off[s] : nullptr;
+        f.rowperm = I.rowperm.ptr() + S.sn_c0[s];
+        f.nr = S.sn_nr[s];
+        f.nc = S.sn_nc[s];
+        f.c0 = S.sn_c0[s];
+        f.child_begin = S.child_ptr[s];
+        f.child_end = S.child_ptr[s + 1];
+        f.parent = S.sn_parent[s];
+        max_front = std::max(max_front, f.nr);
+    }
+    sanm_check(max_front <= 13000,
+               "front of size %u exceeds the shared-memory budget of the solve "
+               "kernels", max_front);
+    I.fd.upload(fd);
+
+    const uint32_t nlev = (uint32_t)S.level_ptr.size() - 1;
+    I.levels.assign(nlev, {});
+    std::vector<Task> asm_t, fwd_t, bwd_t;
+    std::vector<uint32_t> small_l, big_l;
+    for (uint32_t l = 0; l < nlev; ++l) {
+        auto& L = I.levels[l];
+        L.asm_off = (uint32_t)asm_t.size();
+        L.small_off = (uint32_t)small_l.size();
+        L.big_off = (uint32_t)big_l.size();
+        L.fwd_off = (uint32_t)fwd_t.size();
+        L.bwd_off = (uint32_t)bwd_t.size();
+        for (uint32_t q = S.level_ptr[l]; q < S.level_ptr[l + 1]; ++q) {
+            const uint32_t s = S.level_list[q];
+            const uint32_t nr = S.sn_nr[s], nc = S.sn_nc[s], nu = nr - nc;
+            if (S.child_ptr[s + 1] > S.child_ptr[s]) {
+                uint64_t tot = (uint64_t)nr * nr;
+                for (uint64_t t = 0; t * ASM_TILE < tot; ++t) {
+                    asm_t.push_back({s, (uint32_t)t});
+                }
+            }
+            if (nr <= SMALL_NR) {
+                small_l.push_back(s);
+                L.small_max_nr = std::max(L.small_max_nr, nr);
+            } else {
+                big_l.push_back(s);
+                L.big_max_nc = std::max(L.big_max_nc, nc);
+                L.big_max_nr = std::max(L.big_max_nr, nr);
+            }
+            uint32_t nf = std::max<uint32_t>(1, (nu + ROW_CHUNK - 1) / ROW_CHUNK);
+            for (uint32_t t = 0; t < nf; ++t) fwd_t.push_back({s, t});
+            uint32_t nbk = (nc + ROW_CHUNK - 1) / ROW_CHUNK;
+            for (uint32_t t = 0; t < nbk; ++t) bwd_t.push_back({s, t});
+            L.max_nc = std::max(L.max_nc, nc);
+            L.max_nr = std::max(L.max_nr, nr);
+        }
+        L.asm_n = (uint32_t)asm_t.size() - L.asm_off;
+        L.small_n = (uint32_t)small_l.size() - L.small_off;
+        L.big_n = (uint32_t)big_l.size() - L.big_off;
+        L.fwd_n = (uint32_t)fwd_t.size() - L.fwd_off;
+        L.bwd_n = (uint32_t)bwd_t.size() - L.bwd_off;
+    }
+    I.asm_tasks.upload(asm_t);
+    I.fwd_tasks.upload(fwd_t);
+    I.bwd_tasks.upload(bwd_t);
+    I.small_list.upload(small_l);
+    I.big_list.upload(big_l);
+
+    m_stats = {};
+    m_stats.n = n;
+    m_stats.nnz_a = m_nnz;
+    m_stats.factor_entries = S.factor_entries;
+    m_stats.front_entries = S.front_total;
+    m_stats.flops = S.flops;
+    m_stats.nr_supernodes = S.nsn;
+    m_stats.nr_levels = nlev;
+    m_stats.max_front = max_front;
+    m_analyzed = true;
+    I.factored = false;
+}
+
+void SparseLU::factor(const double* vals_dev) {
+    sanm_check(m_analyzed, "factor() before analyze()");
+    Impl& I = *m_impl;
+    if (vals_dev != I.vals.ptr()) {
+        rt::d2d(I.vals.ptr(), vals_dev, m_nnz * sizeof(double));
+    }
+    I.fronts.zero();
+    I.counters.zero();
+    rt::for_each_block(1, 256, 256 * sizeof(double),
+                       AbsMaxKernel{I.vals.ptr(), m_nnz, I.scal.ptr()});
+    rt::for_each(m_nnz, ScatterA{I.fronts.ptr(), I.a_dest.ptr(), I.vals.ptr()});
+    const double* amax = I.scal.ptr();
+    int* npert = I.counters.ptr();
+    for (auto& L : I.levels) {
+        if (L.asm_n) {
+            rt::for_each_block(L.asm_n, 256, 0,
+                               AssembleChildren{I.fd.ptr(), I.child_list.ptr(),
+                                                I.asm_tasks.ptr() + L.asm_off});
+        }
+        if (L.small_n) {
+            size_t smem = (size_t)L.small_max_nr * L.small_max_nr * sizeof(double) + 16;
+            rt::for_each_block(L.small_n, 256, smem,
+                               SmallFrontKernel{I.fd.ptr(),
+                                                I.small_list.ptr() + L.small_off,
+                                                amax, npert});
+        }
+        if (L.big_n) {
+            const uint32_t* list = I.big_list.ptr() + L.big_off;
+            const uint32_t tiles = (L.big_max_nr + 63) / 64;
+            for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
+                rt::for_each_block(
+                        L.big_n, 256,
+                        NB * NB * sizeof(double) + NB * sizeof(uint32_t) + 16,
+                        BigDiagKernel{I.fd.ptr(), list, kb, amax, npert});
+                rt::for_each_block((size_t)L.big_n * tiles, 256,
+                                   (NB * NB + NB * 64) * sizeof(double),
+                                   BigRowPanelKernel{I.fd.ptr(), list, kb, tiles});
+                rt::for_each_block((size_t)L.big_n * tiles * tiles, 256,
+                                   2 * NB * 64 * sizeof(double),
+                                   BigGemmKernel{I.fd.ptr(), list, kb, tiles});
+                rt::for_each_block((size_t)L.big_n * tiles, 256,
+                                   (NB * NB + NB * 64) * sizeof(double),
+                                   BigColPanelKernel{I.fd.ptr(), list, kb, tiles});
+            }
+        }
+    }
+    I.factored = true;
+}
+
+void SparseLU::solve(double* x_dev, const double* b_dev) {
+    Impl& I = *m_impl;
+    sanm_check(I.factored, "solve() before factor()");
+    rt::for_each(m_n, PermuteIn{I.bp.ptr(), b_dev, I.perm.ptr()});
+    for (auto& L : I.levels) {
+        rt::for_each_block(L.fwd_n, 128, 2 * (size_t)L.max_nc * sizeof(double),
+                           ForwardKernel{I.fd.ptr(), I.child_list.ptr(),
+                                         I.fwd_tasks.ptr() + L.fwd_off,
+                                         I.bp.ptr()});
+    }
+    for (size_t l = I.levels.size(); l-- > 0;) {
+        auto& L = I.levels[l];
+        rt::for_each_block(L.bwd_n, 128, (size_t)L.max_nr * sizeof(double),
+                           BackwardKernel{I.fd.ptr(),
+                                          I.bwd_tasks.ptr() + L.bwd_off,
+                                          I.xp.ptr()});
+    }
+    rt::for_each(m_n, PermuteOut{x_dev, I.xp.ptr(), I.perm.ptr()});
+}
+
+void SparseLU::apply(double* y_dev, const double* x_dev) const {
+    const Impl& I = *m_impl;
+    rt::for_each(m_n, SpmvKernel{I.rowptr.ptr(), I.colidx.ptr(), I.vals.ptr(),
+                                 x_dev, y_dev});
+}
+
+void SparseLU::apply_transposed(double*, const double*) const {
+    sanm_throw(SANM_ERR_GENERIC, "apply_transposed is not implemented");
+}
+
+double SparseLU::coeff_l2() const {
+    std::vector<double> v = m_impl->vals.to_host();
+    double s = 0;
+    for (double x : v) s += x * x;
+    return std::sqrt(s);
+}
+
+}  // namespace sanm_b200

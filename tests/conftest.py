@@ -70,10 +70,11 @@ def cuda_impl():
     return sanm_b200.load()
 
 
-@pytest.fixture(scope="session")
+@pytest.fixture(scope="session",
+                params=["hostemu", pytest.param("cuda", marks=pytest.mark.gpu)])
 def impl(request):
-    """CUDA library when a device is present, host emulation otherwise"""
-    if HAS_CUDA:
-        import sanm_b200
-        return sanm_b200.load()
+    """every parity test runs twice: `hostemu` (CPU container, kernel logic) and
+    `cuda` (marked gpu: the product library on the B200, through the C ABI)"""
+    if request.param == "cuda":
+        return request.getfixturevalue("cuda_impl")
     return request.getfixturevalue("hostemu")

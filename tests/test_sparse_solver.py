@@ -1,0 +1,108 @@
+"""SparseSolver: residual-defined parity (the reference's PARDISO is
+a closed third-party binary; its tests pin A x == b and the Tikhonov normal
+equations, tests/tensor.cpp:44-85)."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+from sanm_b200.capi import SparseSolver
+
+
+def build(b, A):
+    A = sp.csr_matrix(A)
+    A.sort_indices()
+    n = A.shape[0]
+    s = SparseSolver(b, n)
+    rows = np.repeat(np.arange(n), np.diff(A.indptr))
+    s.add_constraints(rows, A.indices, A.data)
+    return s
+
+
+def grid_matrix(nx, ny, nz, rng, nonsym=0.0, block=3):
+    """block-structured FEA-like matrix on a 3-D grid (27-point coupling)"""
+    idx = np.arange(nx * ny * nz).reshape(nx, ny, nz)
+    rows, cols = [], []
+    for dx in (-1, 0, 1):
+        for dy in (-1, 0, 1):
+            for dz in (-1, 0, 1):
+                a = idx[max(0, -dx):nx - max(0, dx), max(0, -dy):ny - max(0, dy),
+                        max(0, -dz):nz - max(0, dz)]
+                b = idx[max(0, dx):nx - max(0, -dx), max(0, dy):ny - max(0, -dy),
+                        max(0, dz):nz - max(0, -dz)]
+                rows.append(a.ravel())
+                cols.append(b.ravel())
+    rows = np.concatenate(rows)
+    cols = np.concatenate(cols)
+    nv = nx * ny * nz
+    G = sp.csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(nv, nv))
+    P = sp.kron(G, np.ones((block, block))).tocsr()
+    P.data = rng.uniform(-1, 1, P.nnz)
+    S = (P + P.T) * 0.5 + nonsym * sp.triu(P, 1)
+    # diagonally dominant => well conditioned
+    d = np.asarray(abs(S).sum(axis=1)).ravel()
+    return (S + sp.diags(d * 0.6)).tocsr()
+
+
+def test_reference_8x8(impl, ref):
+    """Tensor.SparseSolver, tests/tensor.cpp:44-85 (random sparse 8x8 + l2)"""
+    rng = np.random.default_rng(7)
+    n = 8
+    A = rng.uniform(-1, 1, (n, n)) * (rng.uniform(0, 1, (n, n)) < 0.5)
+    A += np.diag(rng.uniform(1, 2, n) * 3)
+    bvec = rng.uniform(-1, 1, n)
+    for binding in (impl, ref):
+        s = build(binding, A).prepare()
+        x = s.solve(bvec)
+        np.testing.assert_allclose(A @ x, bvec, atol=1e-12)
+        np.testing.assert_allclose(s.apply(x), bvec, atol=1e-12)
+        assert abs(s.coeff_l2() - np.linalg.norm(A)) < 1e-12
+    xs = []
+    for binding in (impl, ref):
+        s = build(binding, A).prepare(0.3)
+        x = s.solve(bvec)
+        np.testing.assert_allclose((A.T @ A + 0.3 * np.eye(n)) @ x, A.T @ bvec,
+                                   atol=1e-12)
+        xs.append(x)
+    np.testing.assert_allclose(xs[0], xs[1], rtol=1e-10)
+
+
+def test_zero_diagonal_small(impl):
+    """pivoting inside the root front: permuted identity-like system"""
+    A = np.array([[0, 2, 0, 0], [1, 0, 0, 3], [0, 0, 0, 1], [0, 0, 4, 1.]])
+    b = np.array([1., 2., 3., 4.])
+    x = build(impl, A).prepare().solve(b)
+    np.testing.assert_allclose(A @ x, b, atol=1e-13)
+
+
+@pytest.mark.parametrize("shape,nonsym", [((5, 4, 3), 0.0), ((9, 8, 7), 0.3),
+                                          ((16, 12, 10), 0.0)])
+def test_grid_blocks(impl, shape, nonsym):
+    rng = np.random.default_rng(11)
+    A = grid_matrix(*shape, rng, nonsym=nonsym)
+    n = A.shape[0]
+    s = build(impl, A).prepare()
+    st = s.stats()
+    assert st["supernodes"] >= 1 and st["levels"] >= 1
+    for _ in range(2):
+        b = rng.uniform(-1, 1, n)
+        x = s.solve(b)
+        r = A @ x - b
+        scale = abs(A).sum(axis=1).max() * np.abs(x).max() + np.abs(b).max()
+        assert np.abs(r).max() <= 1e-12 * scale
+        xr = spla.spsolve(A.tocsc(), b)
+        assert np.abs(x - xr).max() <= 1e-10 * np.abs(xr).max()
+        np.testing.assert_allclose(s.apply(x), A @ x, rtol=1e-13, atol=1e-13)
+
+
+def test_row_order_and_small_drop(impl):
+    """sparse_solver.cpp:284-305: rows must come in order, tiny entries vanish"""
+    from sanm_b200.capi import SANMAssertionError
+    s = SparseSolver(impl, 3)
+    s.add_constraints([0, 0, 1], [0, 1, 1], [2., 1e-12, 3.])
+    with pytest.raises(SANMAssertionError):
+        s.add_constraints([0], [2], [1.])
+    s.add_constraints([2], [2], [4.])
+    s.prepare()
+    np.testing.assert_allclose(s.solve([2., 3., 4.]), [1, 1, 1], atol=1e-14)
+    assert abs(s.coeff_l2() - np.sqrt(4 + 9 + 16)) < 1e-14

@@ -74,7 +74,7 @@ MATERIAL = mat.MaterialProperty.from_young_poisson(1e6, 0.45)
 
 @pytest.mark.parametrize("energy", [mat.NEOHOOKEAN_I, mat.NEOHOOKEAN_C,
                                     mat.ARAP, mat.STVK_STRETCH])
-def test_pk1_graphs(hostemu, ref, energy):
+def test_pk1_graphs(impl, ref, energy):
     rng = np.random.default_rng(92702102)
     n, order = 37, 20
     xs = make_F_coeffs(rng, n, order)
@@ -86,11 +86,11 @@ def test_pk1_graphs(hostemu, ref, energy):
         F = Ds.batched_matmul(g.constant(dminv))
         return mat.pk1(energy, MATERIAL, F)
 
-    compare(hostemu, ref, build, xs, order)
+    compare(impl, ref, build, xs, order)
 
 
 @pytest.mark.parametrize("energy", [mat.NEOHOOKEAN_I, mat.NEOHOOKEAN_C])
-def test_cauchy_inverse_graphs(hostemu, ref, energy):
+def test_cauchy_inverse_graphs(impl, ref, energy):
     rng = np.random.default_rng(5)
     n, order = 19, 10
     xs = make_F_coeffs(rng, n, order)
@@ -101,10 +101,10 @@ def test_cauchy_inverse_graphs(hostemu, ref, energy):
         F = g.batched_mat_inv_mul(Dm, g.constant(ds), True)
         return mat.cauchy_stress(energy, MATERIAL, F)
 
-    compare(hostemu, ref, build, xs, order)
+    compare(impl, ref, build, xs, order)
 
 
-def test_log_det_xtx(hostemu, ref):
+def test_log_det_xtx(impl, ref):
     """Symbolic.LogDetTaylorProp, tests/symbolic.cpp:640-656"""
     rng = np.random.default_rng(1)
     n, order = 8, 13
@@ -115,10 +115,10 @@ def test_log_det_xtx(hostemu, ref):
         x = g.placeholder()
         return x.batched_transpose().batched_matmul(x).batched_det().log()
 
-    compare(hostemu, ref, build, xs, order)
+    compare(impl, ref, build, xs, order)
 
 
-def test_elemwise_and_reduce(hostemu, ref):
+def test_elemwise_and_reduce(impl, ref):
     """Symbolic.LinearCombination, tests/symbolic.cpp:301-322"""
     rng = np.random.default_rng(2)
     n, order = 9, 8
@@ -130,10 +130,10 @@ def test_elemwise_and_reduce(hostemu, ref):
         return g.linear_combine([(1.2, x.reduce_sum(-1)),
                                  (2.3, x.pow(2. / 3.)), (1.4, x.pow(1.5))], 2.5)
 
-    compare(hostemu, ref, build, xs, order)
+    compare(impl, ref, build, xs, order)
 
 
-def test_matinvmul_nonsquare_matmul(hostemu, ref):
+def test_matinvmul_nonsquare_matmul(impl, ref):
     """Symbolic.MatInvMul / TransMul shapes, tests/symbolic.cpp:179-233,408-426"""
     rng = np.random.default_rng(3)
     n, order = 6, 7
@@ -148,4 +148,4 @@ def test_matinvmul_nonsquare_matmul(hostemu, ref):
         z = g.batched_mat_inv_mul(x * x, y, True)
         return z.batched_matmul(g.constant(c)).batched_transpose()
 
-    compare(hostemu, ref, build, xs, order)
+    compare(impl, ref, build, xs, order)
