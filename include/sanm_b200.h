@@ -218,6 +218,20 @@ int sanm_anm_element_stats(sanm_anm_t* a, double* tet_order_steps,
                            double* element_ms, double* solve_ms,
                            double* factor_ms, double* assemble_ms);
 
+/* statistics of the sparse LU held by this solver */
+int sanm_anm_lu_stats(sanm_anm_t* a, uint64_t* n, uint64_t* nnz_a,
+                      uint64_t* factor_entries, double* flops,
+                      uint64_t* nr_supernodes, uint64_t* nr_levels,
+                      uint64_t* max_front);
+
+/* ---- scalar polynomial helpers of the driver (host): ----------------------
+ * unary_polynomial::roots / solve_eqn, libsanm/unary_polynomial.h:27-47.
+ * f[0] is the constant term; re/im need room for n-1 roots */
+int sanm_poly_roots(const double* f, uint64_t n, int only_real, double* re,
+                    double* im, uint64_t* nr_roots, int* converged);
+int sanm_poly_solve_eqn(const double* f, uint64_t n, double xmin, double xmax,
+                        double b, double eps, double* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,177 @@
+/* sanm_b200/csrc/pade.cpp -- see pade.h. */
+#include "pade.h"
+#include "poly.h"
+#include "rt.h"
+
+#include <cmath>
+#include <limits>
+
+namespace sanm_b200 {
+
+namespace {
+double dot(const double* a, const double* b, size_t n) {
+    double s = 0;
+    for (size_t i = 0; i < n; ++i) s += a[i] * b[i];
+    return s;
+}
+}  // namespace
+
+PadeApproximation::PadeApproximation(std::vector<const double*> xs, size_t len,
+                                     bool anm_cond, bool sanity_check)
+        : m_sanity_check{sanity_check}, m_xs{std::move(xs)}, m_len{len} {
+    const size_t nx = m_xs.size();
+    sanm_check(nx >= 3);
+    if (len < nx * 2 || nx <= 4) return;  // pade.cpp:19-21
+    std::vector<double> astore(nx * nx, 0.0);
+    auto a = [&](int i, int j) -> double& { return astore[i * nx + j]; };
+    const int n = (int)nx - 1;
+    constexpr double eps = std::numeric_limits<double>::epsilon();
+
+    // modified Gram-Schmidt of x_1..x_n (pade.cpp:30-55)
+    std::vector<std::vector<double>> orth(nx);
+    for (int i = 1; i <= n; ++i) {
+        auto& u = orth[i];
+        u.assign(m_xs[i], m_xs[i] + len);
+        for (int j = 1; j < i; ++j) {
+            a(i, j) = dot(m_xs[i], orth[j].data(), len);
+            if (anm_cond && j == 1) {
+                sanm_check(std::fabs(a(i, j)) < 1e-4);
+                a(i, j) = 0;
+            } else {
+                const double f = -a(i, j);
+                const double* o = orth[j].data();
+                for (size_t q = 0; q < len; ++q) u[q] += o[q] * f;
+            }
+        }
+        double aii = std::sqrt(dot(u.data(), u.data(), len));
+        if (aii == 0) {
+            m_d.clear();
+            return;
+        }
+        a(i, i) = aii;
+        double inv = 1 / std::max(aii, eps);
+        for (auto& v : u) v *= inv;
+        if (aii < eps) {
+            double nn = 1 / std::sqrt(dot(u.data(), u.data(), len));
+            for (auto& v : u) v *= nn;
+        }
+    }
+
+    auto solve_d = [&](std::vector<double>& d, int nn) {
+        // pade.cpp:68-92
+        d.assign(nn, 0.0);
+        d[0] = 1;
+        for (int i = 1; i < nn; ++i) {
+            double s = 0;
+            for (int j = 0; j < i; ++j) s += a(nn - j, nn - i) * d[j];
+            double y = a(nn - i, nn - i);
+            d[i] = -s * y / (y * y + 1e-20);
+        }
+        if (m_sanity_check) {
+            for (int i = 1; i < nn; ++i) {
+                double s = 0;
+                for (int j = 0; j <= nn - i; ++j) s += a(nn - j, i) * d[j];
+                sanm_check(std::fabs(s) < 1e-5, "%g", s);
+            }
+        }
+    };
+    solve_d(m_d, n);
+    solve_d(m_d_lo, n - 1);
+
+    m_t_nume_coeffs.assign(n, 0.0);
+    for (int i = 0; i < n; ++i) {
+        double ti = m_xs[i][len - 1];
+        if (!i) {
+            m_t0 = ti;
+        } else {
+            for (int j = 0; j < n - i; ++j) m_t_nume_coeffs[i + j] += m_d[j] * ti;
+        }
+    }
+}
+
+std::vector<double> PadeApproximation::eval_nume(double a, const double* d,
+                                                 int n) const {
+    // pade.cpp:187-194
+    std::vector<double> sum(m_len, 0.0);
+    for (int i = n; i >= 1; --i) {
+        double scale = poly::eval(d, n - i + 1, a);
+        const double* x = m_xs[i];
+        for (size_t q = 0; q < m_len; ++q) sum[q] = sum[q] * a + x[q] * scale;
+    }
+    return sum;
+}
+
+double PadeApproximation::eval_t(double a) const {
+    return poly::eval(m_t_nume_coeffs, a) / poly::eval(m_d, a) + m_t0;
+}
+
+bool PadeApproximation::estimate_valid_range(double start, double eps,
+                                             double limit) {
+    sanm_check(start > 0 && eps > 0);
+    if (m_d.empty()) return false;
+    std::vector<std::complex<double>> rts;
+    if (!poly::roots(m_d, true, rts)) return false;
+    double pole = 0;
+    for (auto& r : rts) {
+        sanm_check(r.imag() == 0);
+        if (r.real() > 0 && (pole == 0 || r.real() < pole)) pole = r.real();
+    }
+    if (pole == 0) pole = start * 4;
+    if (pole <= start) return false;
+
+    const double eps2 = eps * eps;
+    const int n = (int)m_xs.size() - 2;
+    auto check = [&](double a) {
+        double denom_n = poly::eval(m_d, a), denom_lo = poly::eval(m_d_lo, a);
+        std::vector<double> pn = eval_nume(a, m_d.data(), n),
+                            pl = eval_nume(a, m_d_lo.data(), n - 1);
+        const double f = denom_n / denom_lo;
+        double diff2 = 0, pn2 = 0;
+        for (size_t q = 0; q < m_len; ++q) {
+            double v = pl[q] * f - pn[q];
+            diff2 += v * v;
+            pn2 += pn[q] * pn[q];
+        }
+        return diff2 <= pn2 * eps2;
+    };
+    double left = start * 1.001, right = start + (pole - start) * 0.99;
+    if (!check(left)) return false;
+    if (limit && right > limit) right = limit;
+    if (right > start * 2) {
+        if (check(start * 2)) {
+            left = start * 2;
+        } else {
+            right = start * 2;
+        }
+    }
+    int iter = 0;
+    while (iter < 8 && right - left > 1e-3) {
+        double mid = (left + right) / 2;
+        if (check(mid)) {
+            left = mid;
+        } else {
+            right = mid;
+        }
+        ++iter;
+    }
+    m_t_max_a = left;
+    m_t_max = eval_t(left);
+    return true;
+}
+
+double PadeApproximation::solve_a(double t) const {
+    sanm_check(t >= m_t0 && t <= m_t_max);
+    if (t == m_t_max) return m_t_max_a;
+    std::vector<double> c = m_t_nume_coeffs;
+    for (size_t i = 0; i < c.size(); ++i) c[i] -= (t - m_t0) * m_d[i];
+    return poly::solve_eqn(c, 0, m_t_max_a, 0);
+}
+
+std::vector<double> PadeApproximation::eval_xt(double a) const {
+    std::vector<double> ret = eval_nume(a, m_d.data(), (int)m_xs.size() - 2);
+    const double f = a / poly::eval(m_d, a);
+    for (size_t q = 0; q < m_len; ++q) ret[q] = ret[q] * f + m_xs[0][q];
+    return ret;
+}
+
+}  // namespace sanm_b200
