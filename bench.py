@@ -1,0 +1,449 @@
+#!/usr/bin/env python
+"""Headline benchmark: element-Taylor throughput (tet*order steps/s) of the ANM
+inner loop on a synthetic scaled tet cuboid, plus end-to-end solve times of the
+reference's own `fea` configs.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one full series expansion sweep of the element phase over the
+whole tet batch: order-0 evaluation, per-tet Jacobian, and for every order
+k = 1..20 gather (remap_in) -> Taylor propagation (bias phase + coefficient
+phase) -> element-to-node assembly (remap_out); libsanm/anm.cpp:205-290 without
+the global solves (SURVEY 8d metric (i)).  Metric: tets * order per second.
+
+ value    inputs (nodal series x_0..x_K) resident in HBM, device time only
+ e2e      same sweep through the C ABI with HOST buffers: H2D of the nodal
+          series from pinned memory and D2H of the assembled right-hand sides
+          inside the timed region
+ roofline algorithmic bytes of the sweep (8*(S*(k+1)+24) B per
+          tet*order, S = 20/22/27) / device time of the sweep's element
+          kernels, against MEASURED_PEAKS.json hbm_gbs
+ cpu_baseline  the unmodified reference (oracle/_ref, ParallelTaylorCoeffProp)
+          on the host cores, bounded sample
+ solves   end-to-end ANM solve times of the fea configs (GPU path) next to the
+          reference CPU path on the same configs (N=1, rank 0 only)
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ORDER = 20
+S_MIN = {"neohookean_i": 22, "neohookean_c": 20, "arap": 27}
+ORACLE_LIB = os.path.join(ROOT, "oracle", "_ref", "libref_capi.so")
+CONFIG_DIR = os.path.join(ROOT, "oracle", "_ref", "config")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--energy", default="neohookean_c")
+    # per-GPU cuboid (vertices per axis); 201x51x41 -> 2.0 M tets per GPU
+    ap.add_argument("--nx", type=int, default=201)
+    ap.add_argument("--ny", type=int, default=51)
+    ap.add_argument("--nz", type=int, default=41)
+    ap.add_argument("--no-solves", action="store_true",
+                    help="skip the fea end-to-end solve section")
+    ap.add_argument("--no-cpu", action="store_true",
+                    help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-tets", type=int, default=120000,
+                    help="tets of the bounded CPU sample")
+    return ap.parse_args()
+
+
+def algo_bytes_per_sweep(n_tets: int, energy: str, order: int = ORDER) -> float:
+    S = S_MIN[energy]
+    return float(n_tets) * sum(8.0 * (S * (k + 1) + 24)
+                               for k in range(1, order + 1))
+
+
+def make_series(x0: np.ndarray, order: int, seed: int = 92702102):
+    """nodal series: x_0 = rest shape + small perturbation (keeps det F > 0),
+    x_k ~ U(-1,1) * 0.01 * 0.5^k (as tests/pade.cpp:69-71 scales its series)"""
+    rng = np.random.default_rng(seed)
+    n = x0.size
+    x = np.empty((order + 1, n))
+    x[0] = x0 + rng.uniform(-1e-3, 1e-3, n)
+    for k in range(1, order + 1):
+        x[k] = rng.uniform(-1, 1, n) * (0.01 * 0.5 ** k)
+    return x
+
+
+def cuboid_model(binding, nx, ny, nz, energy, spacing=0.025):
+    """the cuboid-twist body of fea/main.cpp:665-690 (both end faces fixed)"""
+    from sanm_b200 import fea, material as mat
+    mesh = fea.TetrahedralMesh.make_cuboid(nx, ny, nz, spacing)
+    body = fea.DeformableBody(
+        binding, mat.MaterialProperty.from_young_poisson(1e7, 0.45), mesh)
+    vx = mesh.vertices[:, 0]
+    body.coord_fixed_mask[(vx <= spacing / 2) |
+                          (vx >= spacing * (nx - 1.5))] = True
+    return mesh, body.make_forward(energy)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,"
+         "clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", "-i", str(self.index),
+                     "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                    capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([s.strip() for s in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self) -> dict:
+        self._stop_evt.set()
+        self.join(timeout=6)
+        mhz, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                 "sw_power_cap"]
+        for s in self.samples:
+            try:
+                mhz.append(float(s[0]))
+                mx = float(s[1])
+            except Exception:
+                continue
+            for nm, v in zip(names, s[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(mhz)) if mhz else None,
+                "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(mhz)}
+
+
+# ------------------------------------------------------------ reference arm
+def load_oracle():
+    from sanm_b200.capi import Binding
+    if not os.path.exists(ORACLE_LIB):
+        raise RuntimeError("oracle/_ref/libref_capi.so is missing "
+                           "(make -C oracle)")
+    return Binding(ctypes.CDLL(ORACLE_LIB), "ref_")
+
+
+def cpu_sample_dims(target_tets: int):
+    """a small cuboid of the same family with about target_tets tets"""
+    c = max(2, round((target_tets / 5 / 4) ** (1 / 3)))
+    return 4 * c + 1, c + 1, c + 1
+
+
+class ReferenceSweep:
+    """the reference's own element phase (ParallelTaylorCoeffProp +
+    SparseLinearDesc::apply, oracle/ref_capi.cpp ref_sweep_run) on the host
+    cores, on a small cuboid of the workload's family"""
+
+    def __init__(self, ref, energy: str, target_tets: int, threads: int):
+        ref.call("set_num_threads", ctypes.c_int(threads))
+        self.ref = ref
+        nx, ny, nz = cpu_sample_dims(target_tets)
+        self.mesh, self.model = cuboid_model(ref, nx, ny, nz, energy)
+        self.x = make_series(self.model.lt_inp.x0, ORDER)
+        self.b = np.empty((ORDER + 1, self.model.lt_inp.nr_unknown_vtx))
+        self.n_tets = self.mesh.nr_tet
+
+    def run(self) -> float:
+        """one sweep; returns its wall seconds"""
+        m = self.model
+        dp = ctypes.POINTER(ctypes.c_double)
+        sec = ctypes.c_double()
+        self.ref.call("sweep_run", m.graph.h, ctypes.c_int(m.y.id),
+                      m.lt_inp.desc.h, m.lt_out.h, ctypes.c_int(ORDER),
+                      self.x.ctypes.data_as(dp), self.b.ctypes.data_as(dp),
+                      ctypes.byref(sec))
+        return sec.value
+
+
+def host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = host_threads()
+    rs = ReferenceSweep(load_oracle(), args.energy, args.cpu_tets, threads)
+    for _ in range(min(args.warmup, 1)):  # a CPU code needs one warm pass
+        rs.run()
+    times = [rs.run() for _ in range(args.steps)]
+    ms = 1e3 * float(np.mean(times))
+    ntet = rs.n_tets
+    value = ntet * ORDER / (ms * 1e-3)
+    sample = (f"cuboid {cpu_sample_dims(args.cpu_tets)} = {ntet} tets, "
+              f"order {ORDER}, {args.energy}: same workload family, bounded")
+    line = {
+        "impl": "reference", "metric": "tet_order_steps_per_s",
+        "value": value, "unit": "tet*order/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, ntet),
+        "cpu_baseline": {"value": value, "unit": "tet*order/s",
+                         "cores": threads, "kind": "reference",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "tet*order/s",
+                "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": ("reference CPU path (unmodified libsanm sources, "
+                 "ParallelTaylorCoeffProp with %d threads, Eigen kernels; MKL "
+                 "unavailable on this box, not on the element path)" % threads),
+    }
+    print(json.dumps(line))
+    sys.stdout.flush()
+    os._exit(0)  # skip the reference's exit-time profiler report on stdout
+
+
+def workload_config(args, tets_per_gpu):
+    return {"workload": ("synthetic scaled tet cuboid (cuboid_twist family), "
+                         "element phase of one order-%d series expansion: "
+                         "gather + Taylor bias/coeff + assembly" % ORDER),
+            "energy_model": args.energy, "order": ORDER,
+            "cuboid_vertices_per_gpu": [args.nx, args.ny, args.nz],
+            "tets_per_gpu": int(tets_per_gpu),
+            "l2": "Taylor stacks per GPU exceed the 126 MB L2 (no flush needed)"}
+
+
+# ------------------------------------------------------------------ our arm
+def pinned_empty(shape):
+    """numpy view of pinned host memory (torch owns the allocation)"""
+    import torch
+    t = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+    return t, t.numpy()
+
+
+def fea_solves(b, ref, cpu_threads):
+    """end-to-end solve times of the reference's fea configs: our GPU path and
+    the reference CPU path through the same front end (sanm_b200/fea.py)"""
+    from sanm_b200 import fea
+    cases = [("bob", "bob.json", []),
+             ("armadillo_small_bend", "armadillo_small.json",
+              ["armadillo_small_bend_override.json"]),
+             ("cuboid_twist_order20", "cuboid_twist.json",
+              ["override_order20.json"])]
+    out = []
+    for name, task, ovs in cases:
+        tpath = os.path.join(CONFIG_DIR, task)
+        if not os.path.exists(tpath):
+            continue
+        ov = [os.path.join(CONFIG_DIR, o) for o in ovs]
+        row = {"config": name}
+        for tag, binding in (("gpu", b), ("cpu_reference", ref)):
+            if binding is None:
+                continue
+            if tag == "cpu_reference":
+                binding.call("set_num_threads", ctypes.c_int(1))
+            log = fea.RunLog(verbose=False)
+            t0 = time.perf_counter()
+            res = fea.run_task(binding, tpath, ov, save=False, log=log)
+            wall = time.perf_counter() - t0
+            st = res[1]
+            if isinstance(st, list):  # cuboid twist: one dict per stage
+                tsolve = sum(s["time"] for s in st)
+                iters = [s["iter_tot"] for s in st]
+                frms = st[-1]["force_rms_recomp"]
+            else:
+                tsolve = st.get("time_solve", st.get("time"))
+                iters = st.get("iter", st.get("iter_tot"))
+                frms = st["force_rms_recomp"]
+            row[tag] = {"solve_s": tsolve, "wall_s": wall, "anm_iters": iters,
+                        "force_rms": frms}
+        if "gpu" in row and "cpu_reference" in row:
+            row["iters_match"] = (row["gpu"]["anm_iters"] ==
+                                  row["cpu_reference"]["anm_iters"])
+        out.append(row)
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import sanm_b200
+    from sanm_b200.capi import ElementSweep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(
+            "cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    b = sanm_b200.load()
+    b.call("set_device", ctypes.c_int(local_rank))
+    stream = torch.cuda.current_stream()
+    b.call("set_stream", ctypes.c_void_p(stream.cuda_stream))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- workload: every rank owns one cuboid shard of identical size (weak)
+    mesh, model = cuboid_model(b, args.nx, args.ny, args.nz, args.energy)
+    n_tets = mesh.nr_tet
+    n = model.lt_inp.nr_unknown_vtx
+    sweep = ElementSweep(model.y, model.lt_inp.desc, model.lt_out, ORDER)
+    x_t, x_host = pinned_empty((ORDER + 1, n))
+    x_host[:] = make_series(model.lt_inp.x0, ORDER, seed=92702102 + rank)
+    b_t, b_host = pinned_empty((ORDER + 1, n))
+    sweep.set_x(x_host)
+    st = sweep.stats()
+
+    # ---- value: device-resident
+    for _ in range(args.warmup):
+        sweep.run()
+    barrier()
+    b.prof_reset()
+    launches0 = b.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        sweep.run()
+    ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = b.launch_count() - launches0
+    prof = {t: b.prof_get(t) for t in
+            ("taylor_next_order", "push_xi", "remap_out", "k_order_bias",
+             "k_order_coef", "k_order_eval", "k_jacobian")}
+    clocks = sampler.stop()
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    sweep.set_x(x_host)
+    sweep.run()
+    sweep.get_b(b_host)
+    barrier()
+    ev2, ev3 = torch.cuda.Event(True), torch.cuda.Event(True)
+    ev2.record(stream)
+    for _ in range(args.steps):
+        sweep.set_x(x_host)
+        sweep.run()
+        sweep.get_b(b_host)
+    ev3.record(stream)
+    barrier()
+    ms_e2e = ev2.elapsed_time(ev3)
+    checksum = float(np.abs(b_host).sum())
+    assert np.isfinite(checksum) and checksum > 0
+
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = (float(v) for v in t.cpu())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    steps_done = float(n_tets) * ORDER * args.steps * world
+    value = steps_done / (ms_total * 1e-3)
+    e2e = steps_done / (ms_e2e * 1e-3)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    elem_ms = sum(prof[t][0] for t in ("taylor_next_order", "push_xi",
+                                       "remap_out")) / args.steps
+    algo = algo_bytes_per_sweep(n_tets, args.energy)
+    achieved = algo / (elem_ms * 1e-3) / 1e9
+    line = {
+        "metric": "tet_order_steps_per_s", "value": value,
+        "unit": "tet*order/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, n_tets),
+        "e2e": {"value": e2e, "unit": "tet*order/s",
+                "h2d_bytes_per_step": int(x_host.nbytes),
+                "d2h_bytes_per_step": int(b_host.nbytes)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": None,
+            "peak_source": ("MEASURED_PEAKS.json hbm_gbs (measured)"
+                            if peaks else "fallback 6650 GB/s"),
+            "kernel": "element order-step kernels of one sweep "
+                      "(bias + coeff phases, gather, assembly)",
+            "algorithmic_bytes_per_sweep": algo,
+            "element_ms_per_sweep": elem_ms,
+            "state_doubles_impl": st["state_doubles"],
+            "state_doubles_min": S_MIN[args.energy],
+            "arena_bytes": st["arena_bytes"],
+            "kernel_ms": {k: {"ms_per_sweep": v[0] / args.steps,
+                              "launches_per_sweep": v[1] / args.steps}
+                          for k, v in prof.items() if v[1]},
+        },
+    }
+    ref = None
+    if os.path.exists(ORACLE_LIB):
+        ref = load_oracle()
+    if world == 1 and not args.no_cpu and ref is not None:
+        threads = host_threads()
+        rs = ReferenceSweep(ref, args.energy, args.cpu_tets, threads)
+        rs.run()
+        sec = min(rs.run() for _ in range(2))
+        ntet = rs.n_tets
+        line["cpu_baseline"] = {
+            "value": ntet * ORDER / sec, "unit": "tet*order/s",
+            "cores": threads, "kind": "reference",
+            "sample": (f"cuboid {cpu_sample_dims(args.cpu_tets)} = {ntet} tets,"
+                       f" order {ORDER}, {args.energy}; unmodified reference "
+                       f"ParallelTaylorCoeffProp, {threads} threads, "
+                       f"{sec:.2f} s per sweep")}
+    if world == 1 and not args.no_solves:
+        b.call("set_stream", ctypes.c_void_p(None))
+        line["solves"] = fea_solves(b, None if args.no_cpu else ref,
+                                    host_threads())
+    print(json.dumps(line))
+    sys.stdout.flush()
+    if world > 1:
+        dist.destroy_process_group()
+    os._exit(0)  # skip the oracle's exit-time profiler report on stdout
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

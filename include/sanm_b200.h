@@ -47,6 +47,10 @@ typedef struct sanm_anm sanm_anm_t;       /* ANMSolverVecScale / ANMEqnSolver /
 const char* sanm_last_error(void);
 /* bind the calling process to a CUDA device (default: device 0) */
 int sanm_set_device(int device);
+/* run every kernel of this library on the caller's CUDA stream (a
+ * cudaStream_t; NULL restores the library's own stream), so that the caller's
+ * events bracket the library's work */
+int sanm_set_stream(void* cuda_stream);
 /* kernels launched by this library since process start */
 uint64_t sanm_launch_count(void);
 /* block until every kernel queued by this library has finished */
@@ -139,6 +143,29 @@ int sanm_remap_identity(int in_rank, const uint64_t* in_dims, int out_rank,
 int sanm_remap_destroy(sanm_remap_t* r);
 /* SparseLinearDesc::apply, anm.h:62 */
 int sanm_remap_apply(sanm_remap_t* r, const double* x, double* y);
+
+/* ---- fused element phase of one series expansion ---------------------------
+ * The element side of ANMDriverHelper::solve_expansion_coeffs
+ * (libsanm/anm.cpp:205-290) with the nodal series x_0..x_K given instead of
+ * solved for: b_0 = remap_out(f(remap_in(x_0))) and, for k = 1..K,
+ *   b_k = remap_out(compute_next_order_bias());  push_xi(remap_in(x_k))
+ * (anm.cpp:207-210, 224-226, 287-290).  Gather, propagation and assembly never
+ * leave the device.  Used by the parity tests and the throughput benchmark. */
+typedef struct sanm_sweep sanm_sweep_t;
+int sanm_sweep_create(sanm_graph_t* g, int f, sanm_remap_t* remap_inp,
+                      sanm_remap_t* remap_out, int order, sanm_sweep_t** out);
+int sanm_sweep_destroy(sanm_sweep_t* s);
+/* x: host [(order+1), n_in] (rows x_0..x_K); copied to the device */
+int sanm_sweep_set_x(sanm_sweep_t* s, const double* x);
+/* one full sweep over orders 0..K on the device (asynchronous) */
+int sanm_sweep_run(sanm_sweep_t* s);
+/* b: host [(order+1), n_out] (rows b_0..b_K); synchronises */
+int sanm_sweep_get_b(sanm_sweep_t* s, double* b);
+/* tet*order steps of one sweep, algorithmic HBM bytes of one sweep (SURVEY 8d:
+ * sum_k 8*(S*(k+1)+24) per tet, S = live Taylor state doubles of the lowered
+ * program) and S itself */
+int sanm_sweep_stats(sanm_sweep_t* s, double* steps, double* algo_bytes,
+                     int* state_doubles, uint64_t* arena_bytes);
 
 /* ---- sparse direct solver: SparseSolver, sparse_solver.h:17-87 ------------ */
 int sanm_sparse_create(uint64_t nr_unknowns, sanm_sparse_t** out);

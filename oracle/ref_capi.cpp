@@ -238,6 +238,55 @@ int ref_graph_concat(Graph* g, int n, const int* vars, int axis, int* out) {
     });
 }
 
+/* ---------------- element sweep (timed CPU baseline) ----------------
+ * The element side of ANMDriverHelper::solve_expansion_coeffs
+ * (libsanm/anm.cpp:205-290) run with the reference's own
+ * ParallelTaylorCoeffProp (libsanm/symbolic.h:391-423; worker threads =
+ * sanm::get_num_threads()) and SparseLinearDesc::apply, with x_0..x_K given.
+ * x: [(K+1), n_in]; b: [(K+1), n_out]; seconds: wall time of the loop.
+ * The shared zero/one constant pools are pre-sized first so that the
+ * reference's multi-thread race on TensorStorage::constant<>
+ * (libsanm/tensor.cpp:251-293) cannot trigger. */
+int ref_sweep_run(Graph* g, int f, Remap* rin, Remap* rout, int order,
+                  const double* x, double* b, double* seconds) {
+    return guard([&] {
+        const size_t nin = rin->d->inp_shape().total_nr_elems(),
+                     nout = rout->d->out_shape().total_nr_elems();
+        {
+            size_t big = rin->d->out_shape().total_nr_elems() * 9;
+            TensorND pre{TensorShape{big}};
+            pre.fill_with_inplace(0);
+            pre.fill_with_inplace(1);
+        }
+        auto xk = [&](int k) {
+            uint64_t d[1] = {nin};
+            TensorND t{rin->d->inp_shape()};
+            memcpy(t.woptr(), x + (size_t)k * nin, sizeof(double) * nin);
+            (void)d;
+            return t;
+        };
+        auto t0 = std::chrono::steady_clock::now();
+        // workers attach to the caller's profiler node, which must exist
+        // (libsanm/symbolic.cpp:318-323), as it does inside the driver
+        SANM_SCOPED_PROFILER("solve_expansion_coeffs");
+        ParallelTaylorCoeffProp prop{g->vars.at(f)};
+        TensorND y0 = prop.push_xi(rin->d->apply(xk(0))).gather_yi();
+        export_tensor(rout->d->apply(y0), b);
+        for (int k = 1; k <= order; ++k) {
+            TensorND bk = rout->d->apply(prop.compute_next_order_bias());
+            if (bk.is_zero() || bk.shape().total_nr_elems() != nout) {
+                memset(b + (size_t)k * nout, 0, sizeof(double) * nout);
+            } else {
+                export_tensor(bk, b + (size_t)k * nout);
+            }
+            if (k < order) prop.push_xi(rin->d->apply(xk(k)));
+        }
+        *seconds = std::chrono::duration<double>(
+                           std::chrono::steady_clock::now() - t0)
+                           .count();
+    });
+}
+
 /* ---------------- Taylor propagation ---------------- */
 int ref_prop_create(Graph* g, int out_var, Prop** out) {
     return guard([&] {

@@ -560,3 +560,69 @@ class ANMImplicitSolver(_ANMBase):
         out = np.empty(self._x_shape)
         self.b.call("anm_implicit_fx0", self.h, _ptr(out))
         return out
+
+
+class ElementSweep:
+    """``sanm_sweep_*``: the element phase of one series expansion
+    (libsanm/anm.cpp:205-290 without the solves) resident on the device."""
+
+    def __init__(self, f: SymbolVar, remap_inp: SparseLinearDesc,
+                 remap_out: SparseLinearDesc, order: int):
+        self.b = f.graph.b
+        self.graph = f.graph
+        self.remap_inp, self.remap_out = remap_inp, remap_out
+        self.order = int(order)
+        self.n_in = int(np.prod(remap_inp.inp_shape))
+        self.n_out = int(np.prod(remap_out.out_shape))
+        self.h = C.c_void_p()
+        self.b.call("sweep_create", f.graph.h, C.c_int(f.id), remap_inp.h,
+                    remap_out.h, C.c_int(self.order), C.byref(self.h))
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.b.fn("sweep_destroy")(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def set_x(self, x):
+        x = _f64(x)
+        assert x.shape == (self.order + 1, self.n_in)
+        self.b.call("sweep_set_x", self.h, _ptr(x))
+
+    def run(self):
+        self.b.call("sweep_run", self.h)
+
+    def get_b(self, out=None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.order + 1, self.n_out))
+        self.b.call("sweep_get_b", self.h, _ptr(out))
+        return out
+
+    def stats(self):
+        steps, ab = C.c_double(), C.c_double()
+        sd, arena = C.c_int(), _u64()
+        self.b.call("sweep_stats", self.h, C.byref(steps), C.byref(ab),
+                    C.byref(sd), C.byref(arena))
+        return {"steps": steps.value, "algo_bytes": ab.value,
+                "state_doubles": sd.value, "arena_bytes": arena.value}
+
+
+def reference_sweep(f: SymbolVar, remap_inp: SparseLinearDesc,
+                    remap_out: SparseLinearDesc, x: np.ndarray) -> np.ndarray:
+    """The same sweep written with the reference's public classes
+    (TaylorCoeffProp + SparseLinearDesc::apply), i.e. the loop of
+    libsanm/anm.cpp:205-290 without the solves.  Works on any binding; the
+    tests and the CPU baseline run it on the oracle."""
+    K = x.shape[0] - 1
+    prop = TaylorCoeffProp(f, max_order=max(K, 1))
+    n_out = int(np.prod(remap_out.out_shape))
+    b = np.zeros((K + 1, n_out))
+    prop.push_xi(remap_inp.apply(x[0]))
+    b[0] = remap_out.apply(prop.gather_yi()).reshape(-1)
+    for k in range(1, K + 1):
+        b[k] = remap_out.apply(prop.compute_next_order_bias()).reshape(-1)
+        if k < K:
+            prop.push_xi(remap_inp.apply(x[k]))
+    return b

@@ -580,6 +580,22 @@ void AnmSolver::solve_expansion_coeffs() {
         }
     }
     estimate_valid_range();
+    static const bool verbose = getenv("SANM_VERBOSE") != nullptr;
+    if (verbose) {
+        // same trace as libsanm/anm.cpp:295-309
+        printf("\nbound=%g t=%g\n", m_t_max_a, m_t_max);
+        printf("x(a):");
+        for (int i = 0; i <= K; ++i) {
+            double s2 = 0;
+            const double* p = m_h_xt.data() + (size_t)i * m_ld;
+            for (uint64_t j = 0; j <= n; ++j) s2 += p[j] * p[j];
+            printf(" %.3g", std::sqrt(s2));
+        }
+        printf("\nt(a):");
+        for (double t : m_t_coeffs) printf(" %.3g,", t);
+        printf("\n");
+        fflush(stdout);
+    }
     ++m_iter;
 }
 

@@ -19,6 +19,10 @@ int sanm_set_device(int device) {
     });
 }
 
+int sanm_set_stream(void* cuda_stream) {
+    return capi::guard([&] { rt::set_stream(cuda_stream); });
+}
+
 uint64_t sanm_launch_count(void) { return rt::launch_count(); }
 
 int sanm_synchronize(void) {

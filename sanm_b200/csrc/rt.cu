@@ -16,6 +16,7 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 #ifdef SANM_HOSTEMU
 
 stream_t stream() { return 0; }
+void set_stream(void*) {}
 void sync() {}
 void* dmalloc(size_t bytes) {
     void* p = malloc(bytes ? bytes : 1);
@@ -33,8 +34,8 @@ void hfree_pinned(void* p) { free(p); }
 #else
 
 namespace {
-cudaStream_t g_stream = nullptr;
-bool g_device_ok = false;
+cudaStream_t g_stream = nullptr, g_user_stream = nullptr;
+bool g_device_ok = false, g_use_user_stream = false;
 }  // namespace
 
 void check_device() {
@@ -54,7 +55,15 @@ void check_device() {
 
 stream_t stream() {
     check_device();
-    return g_stream;
+    return g_use_user_stream ? g_user_stream : g_stream;
+}
+
+void set_stream(void* s) {
+    check_device();
+    // finish what is queued on the old stream before switching
+    SANM_CUDA_CHECK(cudaStreamSynchronize(stream()));
+    g_user_stream = static_cast<cudaStream_t>(s);
+    g_use_user_stream = s != nullptr;
 }
 
 void sync() { SANM_CUDA_CHECK(cudaStreamSynchronize(stream())); }

@@ -96,6 +96,8 @@ void check_device();
 
 //! the single stream every kernel of this library is launched on
 stream_t stream();
+//! run on the caller's stream (nullptr: back to the library's own)
+void set_stream(void* cuda_stream);
 void sync();
 
 void* dmalloc(size_t bytes);

@@ -1,0 +1,142 @@
+/* sanm_b200/csrc/sweep.cu -- the element phase of one series expansion as a
+ * device-resident sweep over the orders: gather (remap_in) -> Taylor
+ * propagation -> element-to-node assembly (remap_out), i.e. the element side of
+ * ANMDriverHelper::solve_expansion_coeffs (libsanm/anm.cpp:205-290) with the
+ * nodal series x_0..x_K supplied by the caller.  C ABI: sanm_sweep_*. */
+#include "capi_util.h"
+#include "prof.h"
+
+namespace sanm_b200 {
+
+class ElementSweep {
+public:
+    ElementSweep(std::shared_ptr<const Graph> g, int f,
+                 std::shared_ptr<const Remap> rin,
+                 std::shared_ptr<const Remap> rout, int order)
+            : m_rin{std::move(rin)}, m_rout{std::move(rout)}, m_order{order} {
+        rt::check_device();
+        sanm_check(order >= 1 && order <= taylor::MAX_ORDER, "order=%d", order);
+        m_prop.reset(new TaylorProp{std::move(g), f, order});
+        m_nin = m_rin->nr_in();
+        m_nout = m_rout->nr_out();
+        m_x.alloc((size_t)(order + 1) * m_nin);
+        m_b.alloc((size_t)(order + 1) * m_nout);
+        m_prop->prepare(m_rin->out_shape());
+        sanm_check(m_rout->nr_in() == m_prop->batch() * m_prop->out_elems(),
+                   "remap_out input size does not match the function output");
+    }
+
+    void set_x(const double* x) {
+        rt::h2d(m_x.ptr(), x, m_x.size() * sizeof(double));
+    }
+
+    void run() {
+        const int K = m_order;
+        TaylorProp& p = *m_prop;
+        p.reset();
+        const VecLayout soa_in{p.in_elems(), p.npad()};
+        const VecLayout soa_out{p.out_elems(), p.npad()};
+        {
+            SANM_PROF("push_xi");
+            m_rin->apply(p.input_slot(0), soa_in, m_x.ptr(), VecLayout{});
+            p.push_xi_filled();
+        }
+        {
+            SANM_PROF("remap_out");
+            m_rout->apply(m_b.ptr(), VecLayout{}, p.output_slot(0), soa_out);
+        }
+        for (int k = 1; k <= K; ++k) {
+            {
+                SANM_PROF("taylor_next_order");
+                p.compute_next_order_bias();
+            }
+            {
+                SANM_PROF("remap_out");
+                m_rout->apply(m_b.ptr() + (size_t)k * m_nout, VecLayout{},
+                              p.output_slot(k), soa_out);
+            }
+            if (k < K) {
+                SANM_PROF("push_xi");
+                m_rin->apply(p.input_slot(k), soa_in,
+                             m_x.ptr() + (size_t)k * m_nin, VecLayout{});
+                p.push_xi_filled();
+            }
+        }
+    }
+
+    void get_b(double* b) {
+        rt::d2h(b, m_b.ptr(), m_b.size() * sizeof(double));
+        m_prop->check_device_error();
+    }
+
+    //! doubles of Taylor state per item and order that later orders re-read
+    int state_doubles() const {
+        int s = 0;
+        const Lowered& L = m_prop->lowered();
+        for (auto& v : L.vars) {
+            if (v.needs_stack && !v.is_const) s += v.e;
+        }
+        for (auto& o : L.ops) s += o.eauxk;
+        return s;
+    }
+
+    double steps() const { return (double)m_prop->batch() * m_order; }
+
+    double algo_bytes() const {
+        // B_elem(k) = 8 * (S * (k + 1) + 24) per item
+        const double S = state_doubles();
+        double per_item = 0;
+        for (int k = 1; k <= m_order; ++k) per_item += 8.0 * (S * (k + 1) + 24);
+        return per_item * (double)m_prop->batch();
+    }
+
+    uint64_t arena_bytes() const { return m_prop->arena_bytes(); }
+
+private:
+    std::shared_ptr<const Remap> m_rin, m_rout;
+    int m_order;
+    uint64_t m_nin = 0, m_nout = 0;
+    std::unique_ptr<TaylorProp> m_prop;
+    rt::DBuf<double> m_x, m_b;
+};
+
+}  // namespace sanm_b200
+
+using namespace sanm_b200;
+
+struct sanm_sweep {
+    std::unique_ptr<ElementSweep> s;
+};
+
+extern "C" {
+
+int sanm_sweep_create(sanm_graph_t* g, int f, sanm_remap_t* remap_inp,
+                      sanm_remap_t* remap_out, int order, sanm_sweep_t** out) {
+    return capi::guard([&] {
+        *out = new sanm_sweep{std::make_unique<ElementSweep>(
+                g->g, f, remap_inp->r, remap_out->r, order)};
+    });
+}
+int sanm_sweep_destroy(sanm_sweep_t* s) {
+    delete s;
+    return 0;
+}
+int sanm_sweep_set_x(sanm_sweep_t* s, const double* x) {
+    return capi::guard([&] { s->s->set_x(x); });
+}
+int sanm_sweep_run(sanm_sweep_t* s) {
+    return capi::guard([&] { s->s->run(); });
+}
+int sanm_sweep_get_b(sanm_sweep_t* s, double* b) {
+    return capi::guard([&] { s->s->get_b(b); });
+}
+int sanm_sweep_stats(sanm_sweep_t* s, double* steps, double* algo_bytes,
+                     int* state_doubles, uint64_t* arena_bytes) {
+    return capi::guard([&] {
+        *steps = s->s->steps();
+        *algo_bytes = s->s->algo_bytes();
+        *state_doubles = s->s->state_doubles();
+        *arena_bytes = s->s->arena_bytes();
+    });
+}
+}

@@ -1,6 +1,7 @@
 /* sanm_b200/csrc/taylor.cu -- see taylor.h.  Kernels: one thread per batch item
  * (tetrahedron), walking the lowered operator list (taylor_dev.h). */
 #include "taylor.h"
+#include "prof.h"
 
 namespace sanm_b200 {
 
@@ -249,6 +250,9 @@ const double* TaylorProp::output_slot(int k) const {
 }
 
 void TaylorProp::launch(int k, int phase, int sb_zero) {
+    static const char* const TAGS[] = {"k_order_eval", "k_order_bias",
+                                       "k_order_coef"};
+    SANM_PROF(m_in_jacobian ? "k_jacobian" : TAGS[phase]);
     rt::for_each(m_low.batch, OrderKernel{m_prog, k, phase, sb_zero});
 }
 
@@ -293,6 +297,7 @@ const double* TaylorProp::ensure_jacobian() {
     const int idim = in_elems(), odim = out_elems();
     double* in1 = vbase(m_hvars[m_low.input], 1);
     const double* out1 = vbase(m_hvars[m_low.output], 1);
+    m_in_jacobian = true;
     if (m_low.elemwise) {
         m_jac.ensure(n * odim);
         rt::for_each(n * idim, FillUnit{in1, n, m_npad, -1});
@@ -307,6 +312,7 @@ const double* TaylorProp::ensure_jacobian() {
                          ExtractJacCol{m_jac.ptr(), out1, n, odim, idim, j, m_npad});
         }
     }
+    m_in_jacobian = false;
     m_jac_done = true;
     return m_jac.ptr();
 }

@@ -74,6 +74,7 @@ private:
     std::shared_ptr<const Graph> m_graph;
     int m_out_var, m_max_order;
     bool m_prepared = false, m_xi_known = false, m_jac_done = false;
+    bool m_in_jacobian = false;
     int m_order = -1;  //!< -1: nothing pushed
     int64_t m_npad = 0;
     Lowered m_low;

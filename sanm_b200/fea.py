@@ -1,0 +1,979 @@
+"""Finite-element front end: the host-side mirror of the reference's ``fea``
+application (``fea/main.cpp``, ``fea/mesh*.{h,cpp}``, ``fea/tetrahedral_mesh.*``)
+for the parts that feed the ANM hot path: tetrahedral meshes (TetGen reader,
+``make_cuboid``), the two sparse remaps of a deformable body (node -> per-tet
+shape matrix, per-tet stress -> nodal force), the material graphs and the task
+drivers ``gravity`` / ``mesh_twist`` / ``test_cuboid`` / ``test_cuboid_twist``.
+
+Everything numeric goes through a :class:`sanm_b200.capi.Binding`, i.e. through
+the C ABI of ``include/sanm_b200.h`` -- the same front end can therefore drive
+the oracle (``ref_`` prefix, tests only) on byte-identical meshes, remaps and
+configs, which is how the parity tests are written.
+
+    python -m sanm_b200.fea <sys.json> <task.json> [override.json ...]
+
+mirrors the reference CLI (``fea/main.cpp:1066-1102``); outputs (``.obj`` and
+stats ``.json``) are written to the current directory like the reference does.
+Mesh arrays are ``[V, 3]`` / ``[N, 4]`` row-major (the reference stores the
+transposes as Eigen column-major matrices: same memory).
+"""
+from __future__ import annotations
+
+import json
+import math
+import os
+import sys
+import time
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional
+
+import numpy as np
+
+from . import material as mat
+from .capi import (ANMEqnSolver, ANMImplicitSolver, ANMSolverVecScale, Binding,
+                   Hyper, SparseLinearDesc, SymbolVar)
+
+RMS_THRESH_FORCE_EQU = 1e-10  # fea/main.cpp:28
+
+
+# --------------------------------------------------------------------- mesh
+class TetrahedralMesh:
+    """fea/tetrahedral_mesh.h:24-126"""
+
+    def __init__(self, vertices: np.ndarray, tets: np.ndarray,
+                 surface_vtx: Optional[np.ndarray] = None,
+                 surfaces: Optional[np.ndarray] = None):
+        self.vertices = np.ascontiguousarray(vertices, dtype=np.float64)
+        self.tets = np.ascontiguousarray(tets, dtype=np.int64)
+        assert self.vertices.ndim == 2 and self.vertices.shape[1] == 3
+        assert self.tets.ndim == 2 and self.tets.shape[1] == 4
+        #: sorted unique ids of the vertices on the surface (may be empty)
+        self.surface_vtx = (np.zeros(0, np.int64) if surface_vtx is None else
+                            np.unique(np.asarray(surface_vtx, np.int64)))
+        #: boundary triangles [F, 3] (cuboids only)
+        self.surfaces = (np.zeros((0, 3), np.int64) if surfaces is None else
+                         np.asarray(surfaces, np.int64))
+        self._cache: Dict[str, np.ndarray] = {}
+
+    def copy(self) -> "TetrahedralMesh":
+        return TetrahedralMesh(self.vertices.copy(), self.tets,
+                               self.surface_vtx, self.surfaces)
+
+    @property
+    def nr_vertices(self) -> int:
+        return self.vertices.shape[0]
+
+    @property
+    def nr_tet(self) -> int:
+        return self.tets.shape[0]
+
+    nr_faces = nr_tet
+
+    def _compute(self):
+        """vertex_norms / tet_volumes / shape_matrix,
+        fea/tetrahedral_mesh.cpp:31-72"""
+        if self._cache:
+            return
+        x = self.vertices[self.tets]            # [N, 4, 3]
+        v1 = x[:, 1] - x[:, 0]
+        v2 = x[:, 2] - x[:, 0]
+        v3 = x[:, 3] - x[:, 0]
+        t1 = np.cross(v2, v3)
+        t2 = np.cross(v3, v1)
+        t3 = np.cross(v1, v2)
+        det = np.einsum("ij,ij->i", v1, t1)
+        sgn = np.where(det > 0, -1.0, 1.0)[:, None]
+        t1, t2, t3 = t1 * sgn, t2 * sgn, t3 * sgn
+        norms = np.stack([-(t1 + t2 + t3), t1, t2, t3], axis=1) * (1.0 / 6)
+        # shape matrix: columns are v1, v2, v3 (row-major [N, 3, 3])
+        self._cache["shape"] = np.ascontiguousarray(
+            np.stack([v1, v2, v3], axis=2))
+        self._cache["norms"] = np.ascontiguousarray(norms)  # [N, 4, 3]
+        self._cache["vol"] = np.abs(det) / 6
+
+    @property
+    def vertex_norms(self) -> np.ndarray:
+        self._compute()
+        return self._cache["norms"]
+
+    @property
+    def tet_volumes(self) -> np.ndarray:
+        self._compute()
+        return self._cache["vol"]
+
+    @property
+    def shape_matrix(self) -> np.ndarray:
+        self._compute()
+        return self._cache["shape"]
+
+    def clear_cache(self):
+        self._cache = {}
+
+    def resize_inplace(self, scale: float):
+        self.vertices *= scale
+        self.clear_cache()
+
+    def replace_vtx(self, vtx: np.ndarray):
+        assert vtx.shape == self.vertices.shape
+        self.vertices = np.array(vtx, dtype=np.float64)
+        self.clear_cache()
+
+    def replace_with_mask(self, fixed_mask: np.ndarray, value: np.ndarray):
+        replace_with_mask(self.vertices, fixed_mask, value)
+        self.clear_cache()
+
+    def apply_vtx_delta(self, delta: np.ndarray):
+        self.vertices += delta
+        self.clear_cache()
+
+    # ------------------------------------------------------------ builders
+    @staticmethod
+    def make_cuboid(nx: int, ny: int, nz: int, size: float
+                    ) -> "TetrahedralMesh":
+        """fea/tetrahedral_mesh.cpp:92-205 (5 tets per hexahedron), vectorised;
+        vertex and element numbering are the reference's"""
+        assert nx >= 2 and ny >= 2 and nz >= 2 and size > 0
+        ii, jj, kk = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz),
+                                 indexing="ij")
+        vertex = np.stack([ii, jj, kk], -1).reshape(-1, 3) * float(size)
+        on_surf = ((ii == 0) | (ii == nx - 1) | (jj == 0) | (jj == ny - 1) |
+                   (kk == 0) | (kk == nz - 1)).reshape(-1)
+
+        def vid(x, y, z):
+            return (x * ny + y) * nz + z
+
+        ci, cj, ck = np.meshgrid(np.arange(nx - 1), np.arange(ny - 1),
+                                 np.arange(nz - 1), indexing="ij")
+        ci, cj, ck = ci.reshape(-1), cj.reshape(-1), ck.reshape(-1)
+        hexid = np.stack([vid(ci, cj, ck), vid(ci + 1, cj, ck),
+                          vid(ci + 1, cj + 1, ck), vid(ci, cj + 1, ck),
+                          vid(ci, cj, ck + 1), vid(ci + 1, cj, ck + 1),
+                          vid(ci + 1, cj + 1, ck + 1), vid(ci, cj + 1, ck + 1)],
+                         axis=1)                                # [H, 8]
+        local = np.array([[0, 2, 1, 5], [0, 4, 7, 5], [0, 2, 5, 7],
+                          [2, 6, 5, 7], [0, 7, 3, 2]])
+        tets = hexid[:, local].reshape(-1, 4)
+        # boundary triangles, in the order the reference emits them
+        faces: List[np.ndarray] = []
+        order: List[np.ndarray] = []
+        specs = [(ci == 0, [(3, 0, 7), (7, 0, 4)]),
+                 (ci == nx - 2, [(1, 2, 6), (6, 5, 1)]),
+                 (cj == 0, [(0, 1, 5), (0, 5, 4)]),
+                 (cj == ny - 2, [(7, 6, 3), (6, 2, 3)]),
+                 (ck == 0, [(1, 3, 2), (0, 3, 1)]),
+                 (ck == nz - 2, [(4, 5, 7), (7, 5, 6)])]
+        slot = 0
+        for cond, tris in specs:
+            sel = np.nonzero(cond)[0]
+            for tri in tris:
+                faces.append(hexid[sel][:, list(tri)])
+                order.append(sel * 12 + slot)
+                slot += 1
+        faces_all = np.concatenate(faces)
+        perm = np.argsort(np.concatenate(order), kind="stable")
+        return TetrahedralMesh(vertex, tets, np.nonzero(on_surf)[0],
+                               faces_all[perm])
+
+    @staticmethod
+    def from_tetgen_files(filebase: str) -> "TetrahedralMesh":
+        """fea/tetrahedral_mesh.cpp:206-258"""
+
+        def tokens(path):
+            with open(path) as f:
+                txt = [ln.split("#", 1)[0] for ln in f]
+            return " ".join(txt).split()
+
+        tn = tokens(filebase + ".node")
+        nr_vtx, dim, nr_attr, bmark = (int(t) for t in tn[:4])
+        assert dim == 3 and not nr_attr and not bmark
+        node = np.array(tn[4:4 + nr_vtx * 4], dtype=np.float64).reshape(-1, 4)
+        assert np.array_equal(node[:, 0], np.arange(nr_vtx)), \
+            "vertex ids must be 0..n-1"
+        te = tokens(filebase + ".ele")
+        nr_tet, npt, nr_attr = (int(t) for t in te[:3])
+        assert npt == 4 and not nr_attr
+        ele = np.array(te[3:3 + nr_tet * 5], dtype=np.int64).reshape(-1, 5)
+        assert np.array_equal(ele[:, 0], np.arange(nr_tet))
+        tf = tokens(filebase + ".face")
+        nr_face, bmark = int(tf[0]), int(tf[1])
+        w = 5 if bmark else 4
+        face = np.array(tf[2:2 + nr_face * w], dtype=np.int64).reshape(-1, w)
+        return TetrahedralMesh(node[:, 1:4], ele[:, 1:5],
+                               np.unique(face[:, 1:4]))
+
+    # ------------------------------------------------------------- output
+    def write_obj(self, path: str, filter_set: Optional[np.ndarray] = None,
+                  vertices: Optional[np.ndarray] = None):
+        """fea/tetrahedral_mesh.cpp:260-368"""
+        V = self.vertices if vertices is None else vertices
+        with open(path, "w") as fout:
+            if filter_set is None and len(self.surfaces):
+                used, inv = np.unique(self.surfaces.reshape(-1),
+                                      return_inverse=True)
+                # the reference numbers vertices in order of first use
+                first = np.full(len(used), len(inv), np.int64)
+                np.minimum.at(first, inv, np.arange(len(inv)))
+                order = np.argsort(first, kind="stable")
+                rank = np.empty_like(order)
+                rank[order] = np.arange(len(order))
+                for v in V[used[order]]:
+                    fout.write("v %g %g %g\n" % tuple(v))
+                for f in rank[inv].reshape(-1, 3) + 1:
+                    fout.write("f %d %d %d\n" % tuple(f))
+                return
+            if filter_set is None and len(self.surface_vtx):
+                filter_set = self.surface_vtx
+            T = self.tets.copy()
+            x = V[T]
+            det = np.einsum("ij,ij->i", x[:, 1] - x[:, 0],
+                            np.cross(x[:, 2] - x[:, 0], x[:, 3] - x[:, 0]))
+            swap = det > 0
+            T[swap, 1], T[swap, 2] = T[swap, 2].copy(), T[swap, 1].copy()
+            facets = np.stack([T[:, [0, 1, 2]], T[:, [1, 3, 2]],
+                               T[:, [1, 0, 3]], T[:, [0, 2, 3]]],
+                              axis=1).reshape(-1, 3)
+            if filter_set is not None:
+                keep = np.zeros(len(V), bool)
+                keep[np.asarray(filter_set)] = True
+                idmap = np.cumsum(keep) - 1
+                for v in V[keep]:
+                    fout.write("v %g %g %g\n" % tuple(v))
+                facets = facets[keep[facets].all(axis=1)]
+                facets = idmap[facets]
+            else:
+                for v in V:
+                    fout.write("v %g %g %g\n" % tuple(v))
+            for f in facets + 1:
+                fout.write("f %d %d %d\n" % tuple(f))
+
+
+def replace_with_mask(dst: np.ndarray, fixed_mask: np.ndarray,
+                      src: np.ndarray):
+    """fea/mesh.cpp:14-24: write src into the non-fixed entries of dst"""
+    free = ~fixed_mask
+    assert int(free.sum()) == np.size(src), "src size mismatch"
+    dst[free] = np.asarray(src).reshape(-1)
+
+
+# ------------------------------------------------------------------ remaps
+@dataclass
+class ShapeMatTrans:
+    """MeshShapeMatTrans, fea/mesh.h:79-132 + fea/mesh_template.h:19-127:
+    unknown nodal coordinates (+ t) -> per-tet shape matrix minus ``bias``"""
+    desc: SparseLinearDesc
+    bias: np.ndarray            # [N, 3, 3]
+    x0: np.ndarray              # [nr_unknown_vtx]
+    vertex_loc: np.ndarray      # [nr_unknown_vtx, 2] = (vtx, coord)
+    has_delta: bool
+    rowptr: np.ndarray
+    idx: np.ndarray
+    coeff: np.ndarray
+
+    @property
+    def nr_unknown_vtx(self) -> int:
+        return len(self.x0)
+
+    def copy_vtx_values(self, vtx_values: np.ndarray) -> np.ndarray:
+        return np.ascontiguousarray(
+            vtx_values[self.vertex_loc[:, 0], self.vertex_loc[:, 1]])
+
+
+def build_shape_mat_csr(mesh: TetrahedralMesh, fixed_mask: np.ndarray,
+                        init_vtx_coord: Optional[np.ndarray],
+                        vtx_delta: Optional[np.ndarray]):
+    """CSR of MeshShapeMatTrans (fea/mesh_template.h:19-111); entry order per
+    row is the reference's: -x[v0], +x[v_dm], delta*t"""
+    V, N = mesh.nr_vertices, mesh.nr_tet
+    assert fixed_mask.shape == (V, 3)
+    init = mesh.vertices if init_vtx_coord is None else init_vtx_coord
+    free = ~fixed_mask
+    nr_unknown = int(free.sum())
+    vtx2uidx = np.where(free, np.cumsum(free.reshape(-1)).reshape(V, 3) - 1, -1)
+    vertex_loc = np.argwhere(free)
+    x0 = np.ascontiguousarray(init[free])
+    T = mesh.tets
+    v0 = T[:, 0]                                  # [N]
+    vi = T[:, 1:4]                                # [N, dm]
+    # arrays indexed [ele, r, dm]
+    u0 = np.broadcast_to(vtx2uidx[v0][:, :, None], (N, 3, 3))
+    ui = np.transpose(vtx2uidx[vi], (0, 2, 1))
+    x0v = np.broadcast_to(init[v0][:, :, None], (N, 3, 3))
+    xiv = np.transpose(init[vi], (0, 2, 1))
+    bias = np.where(u0 < 0, -x0v, 0.0) + np.where(ui < 0, xiv, 0.0)
+    cand_idx = np.stack([u0, ui, np.full((N, 3, 3), nr_unknown)], axis=-1)
+    cand_coef = np.stack([np.full((N, 3, 3), -1.0), np.full((N, 3, 3), 1.0),
+                          np.zeros((N, 3, 3))], axis=-1)
+    valid = np.stack([u0 >= 0, ui >= 0, np.zeros((N, 3, 3), bool)], axis=-1)
+    if vtx_delta is not None:
+        d = (np.transpose(vtx_delta[vi], (0, 2, 1)) -
+             vtx_delta[v0][:, :, None])
+        cand_coef[..., 2] = d
+        valid[..., 2] = d != 0
+    counts = valid.sum(axis=-1).reshape(-1)
+    rowptr = np.zeros(N * 9 + 1, np.uint64)
+    np.cumsum(counts, out=rowptr[1:])
+    idx = cand_idx[valid].astype(np.uint64)
+    coeff = cand_coef[valid]
+    return (rowptr, idx, coeff, np.ascontiguousarray(bias), x0, vertex_loc,
+            nr_unknown)
+
+
+def build_force_out_csr(mesh: TetrahedralMesh, vertex_loc: np.ndarray):
+    """CSR of MeshForceOutputTrans (fea/mesh_template.h:131-161): nodal force =
+    sum over adjacent tets of stress times the area-weighted vertex normal"""
+    N, V = mesh.nr_tet, mesh.nr_vertices
+    flat_v = mesh.tets.reshape(-1)              # index = ele*4 + vtx_id
+    order = np.argsort(flat_v, kind="stable")   # MeshVertexReverseList order
+    deg = np.bincount(flat_v, minlength=V)
+    assert deg.min() > 0, "dangling vertex"
+    vptr = np.zeros(V + 1, np.int64)
+    np.cumsum(deg, out=vptr[1:])
+    uv, uc = vertex_loc[:, 0], vertex_loc[:, 1]
+    n_unknown = len(uv)
+    cnt = deg[uv]
+    rowptr = np.zeros(n_unknown + 1, np.uint64)
+    np.cumsum(cnt * 3, out=rowptr[1:])
+    # expand (unknown, adjacent item)
+    tot = int(cnt.sum())
+    rep_u = np.repeat(np.arange(n_unknown), cnt)
+    start = np.repeat(vptr[uv], cnt)
+    first = np.repeat(np.cumsum(cnt) - cnt, cnt)
+    item = order[start + (np.arange(tot) - first)]          # ele*4 + vtx_id
+    ele = item // 4
+    norm = mesh.vertex_norms.reshape(-1, 3)[item]           # [tot, 3]
+    coord = uc[rep_u]
+    idx = (ele * 9 + coord * 3)[:, None] + np.arange(3)[None, :]
+    return rowptr, idx.reshape(-1).astype(np.uint64), \
+        np.ascontiguousarray(norm.reshape(-1))
+
+
+@dataclass
+class ElasticForceModel:
+    """fea/mesh.h:154-160"""
+    graph: object
+    y: SymbolVar
+    potential: Optional[SymbolVar]
+    lt_inp: ShapeMatTrans
+    lt_out: SparseLinearDesc
+
+
+class DeformableBody:
+    """TetrahedralDeformableBody, fea/mesh.h:149-226"""
+
+    def __init__(self, b: Binding, material: mat.MaterialProperty,
+                 mesh: TetrahedralMesh):
+        self.b = b
+        self.material = material
+        self.mesh = mesh
+        self.coord_fixed_mask = np.zeros((mesh.nr_vertices, 3), bool)
+
+    def _remaps(self, init_vtx_coord, vtx_delta):
+        b, mesh = self.b, self.mesh
+        (rowptr, idx, coeff, bias, x0, vloc, nu) = build_shape_mat_csr(
+            mesh, self.coord_fixed_mask, init_vtx_coord, vtx_delta)
+        has_delta = vtx_delta is not None
+        desc = SparseLinearDesc(b, (mesh.nr_tet, 3, 3), (nu + has_delta,),
+                                rowptr, idx, coeff)
+        lt_inp = ShapeMatTrans(desc, bias, x0, vloc, has_delta, rowptr, idx,
+                               coeff)
+        orow, oidx, ocoef = build_force_out_csr(mesh, vloc)
+        lt_out = SparseLinearDesc(b, (nu,), (mesh.nr_tet, 3, 3), orow, oidx,
+                                  ocoef)
+        return lt_inp, lt_out
+
+    def make_forward(self, energy_model: str,
+                     init_vtx_coord: Optional[np.ndarray] = None,
+                     vtx_delta: Optional[np.ndarray] = None
+                     ) -> ElasticForceModel:
+        """fea/mesh_template.h:191-219"""
+        lt_inp, lt_out = self._remaps(init_vtx_coord, vtx_delta)
+        g = self.b.ComputingGraph()
+        Ds = g.placeholder() + g.constant(lt_inp.bias)
+        DmInv = g.constant(np.linalg.inv(self.mesh.shape_matrix))
+        F = Ds.batched_matmul(DmInv)
+        P = mat.pk1(energy_model, self.material, F, 3)
+        pot = mat.elastic_potential_density(energy_model, self.material, F, 3)
+        if pot is not None:
+            pot = pot * g.constant(self.mesh.tet_volumes.reshape(-1, 1))
+        return ElasticForceModel(g, P, pot, lt_inp, lt_out)
+
+    def make_inverse(self, energy_model: str) -> ElasticForceModel:
+        """fea/mesh_template.h:172-189"""
+        lt_inp, lt_out = self._remaps(None, None)
+        g = self.b.ComputingGraph()
+        Dm = g.placeholder() + g.constant(lt_inp.bias)
+        Ds = g.constant(self.mesh.shape_matrix)
+        F = g.batched_mat_inv_mul(Dm, Ds, True)
+        sigma = mat.cauchy_stress(energy_model, self.material, F, 3)
+        return ElasticForceModel(g, sigma, None, lt_inp, lt_out)
+
+    @staticmethod
+    def compute_force_rms(model: ElasticForceModel, xt: np.ndarray,
+                          f_load: np.ndarray, final_mesh: TetrahedralMesh,
+                          sanity_check: bool) -> float:
+        """fea/mesh_template.h:221-237"""
+        sym_inpval = model.lt_inp.desc.apply(xt)
+        shape0 = sym_inpval + model.lt_inp.bias
+        assert_allclose("shape matrix check", shape0, final_mesh.shape_matrix)
+        stress = model.graph.eval_unary_func(model.y, sym_inpval)
+        internal = model.lt_out.apply(stress)
+        if sanity_check:
+            assert_allclose("force equilibrium check", internal, -f_load, 1e-5)
+        return norm_rms(internal + f_load)
+
+
+def norm_rms(x: np.ndarray) -> float:
+    x = np.asarray(x).reshape(-1)
+    return float(math.sqrt(np.dot(x, x) / x.size))
+
+
+def assert_allclose(msg, a, b, eps=1e-4):
+    """TensorND::assert_allclose, libsanm/tensor.cpp:670-684"""
+    a, b = np.asarray(a), np.asarray(b)
+    den = np.maximum(np.minimum(np.abs(a), np.abs(b)), 1.0)
+    err = np.abs(a - b) / den
+    if not (err.max() <= eps):
+        raise AssertionError(f"{msg}: max err {err.max():g} > {eps:g}")
+
+
+# ------------------------------------------------------------------ drivers
+def setup_solver_param(config: dict, **kw) -> Hyper:
+    """fea/main.cpp:105-120"""
+    return Hyper(order=int(config.get("order", 20)),
+                 xcoeff_l2_penalty=float(config.get("xcoeff_l2_penalty", 0)),
+                 use_pade=int(not config.get("disable_pade", False)),
+                 sanity_check=int(not config.get("disable_anm_sanity_check",
+                                                 False)), **kw)
+
+
+@dataclass
+class RunLog:
+    """what the reference prints to stdout, kept for parity checks"""
+    residuals: List[float] = field(default_factory=list)
+    t_uppers: List[float] = field(default_factory=list)
+    total_nr_iter: int = 0
+    verbose: bool = True
+
+    def say(self, s: str):
+        if self.verbose:
+            sys.stdout.write(s)
+            sys.stdout.flush()
+
+
+def run_anm_eqn(solver: ANMEqnSolver, log: RunLog) -> np.ndarray:
+    """fea/main.cpp:172-190"""
+    while True:
+        r = solver.residual_rms()
+        log.residuals.append(r)
+        log.say(" %.2g" % r)
+        if solver.converged():
+            break
+        solver.next_iter()
+    it = solver.get_nr_iter()
+    log.total_nr_iter += it
+    log.say(" iter=%d\n" % it)
+    return solver.get_x()
+
+
+def run_anm_implicit(solver: ANMImplicitSolver, log: RunLog, t_dest=1.0,
+                     callback: Optional[Callable] = None) -> np.ndarray:
+    """fea/main.cpp:192-215"""
+    while True:
+        tu = solver.get_t_upper()
+        log.t_uppers.append(tu)
+        log.say(" %.2g" % tu)
+        if callback:
+            callback(solver)
+        if tu >= t_dest:
+            break
+        solver.update_approx()
+    it = solver.get_nr_iter()
+    log.total_nr_iter += it
+    log.say(" iter=%d\n" % it)
+    return solver.eval(solver.solve_a(t_dest))[0]
+
+
+def relative_displacement(v0: np.ndarray, v1: np.ndarray) -> float:
+    """fea/main.cpp:217-223"""
+    d = math.sqrt(((v1 - v0) ** 2).sum() / v0.size)
+    return d / float(np.linalg.norm(v0.max(axis=0) - v0.min(axis=0)))
+
+
+def get_nr_inverted(tets, v0, v1) -> int:
+    """fea/main.cpp:225-244"""
+
+    def sign(v):
+        x = v[tets]
+        a, b_, c = x[:, 1] - x[:, 0], x[:, 2] - x[:, 0], x[:, 3] - x[:, 0]
+        return np.einsum("ij,ij->i", np.cross(a, b_), c) >= 0
+
+    return int((sign(v0) != sign(v1)).sum())
+
+
+def make_material_property(cfg: dict, need_density=False
+                           ) -> mat.MaterialProperty:
+    """fea/main.cpp:135-149"""
+    if cfg["type"] != "young_poisson":
+        raise RuntimeError(f"unknown material type {cfg['type']}")
+    m = mat.MaterialProperty.from_young_poisson(float(cfg["young"]),
+                                                float(cfg["poisson"]))
+    if need_density or "density" in cfg:
+        m.density = float(cfg["density"])
+    return m
+
+
+def run_and_save(name: str, config: dict, deformable: DeformableBody,
+                 inverse_mode: bool, f_load_full: np.ndarray, save=True,
+                 log: Optional[RunLog] = None):
+    """fea/main.cpp:247-433 (ANM path; the Newton/LM competitor under
+    ``baseline`` is out of scope).  Returns (out_mesh, stats)."""
+    log = log or RunLog()
+    log.say("solving %s%s " % (name, " (inv)" if inverse_mode else ""))
+    jstat: dict = {}
+    t0 = time.perf_counter()
+    energy = config["energy_model"]
+    model = (deformable.make_inverse(energy) if inverse_mode else
+             deformable.make_forward(energy))
+    f_load_sub = model.lt_inp.copy_vtx_values(f_load_full)
+
+    def make_out_mesh(xt):
+        m = deformable.mesh.copy()
+        m.replace_with_mask(deformable.coord_fixed_mask, xt)
+        return m
+
+    jstat["time_prep"] = time.perf_counter() - t0
+    if "baseline" in config:
+        raise RuntimeError("the Newton/LM baseline solver is out of scope")
+    iter_begin = log.total_nr_iter
+    t0 = time.perf_counter()
+    hyper = setup_solver_param(config, converge_rms=RMS_THRESH_FORCE_EQU,
+                               solution_check_tol=1e-3)
+    if config.get("save_interm", False):
+        hyper.solution_check_tol = 0.01
+        solver = ANMSolverVecScale(model.y, model.lt_inp.desc, model.lt_out,
+                                   model.lt_inp.x0, 0.0, f_load_sub, hyper)
+        log.say("interm: ")
+        tnext, it, xt = 0.05, 1, None
+        while tnext < 1:
+            while tnext <= 1.02 and solver.get_t_upper() >= tnext:
+                xt = solver.eval(solver.solve_a(tnext))[0]
+                if save:
+                    make_out_mesh(xt).write_obj(
+                        "%s-%.2f.obj" % (config["out_filename"], tnext))
+                log.say(" %g" % tnext)
+                tnext += 0.05
+            if tnext >= 1:
+                break
+            solver.update_approx()
+            it += 1
+        log.total_nr_iter += solver.get_nr_iter()
+    else:
+        log.say("order=%d:" % hyper.order)
+        solver = ANMEqnSolver(model.y, model.lt_inp.desc, model.lt_out,
+                              model.lt_inp.x0, f_load_sub, hyper)
+        xt = run_anm_eqn(solver, log)
+    jstat["time_solve"] = time.perf_counter() - t0
+    log.say("timing(sec): prep=%.3f solve=%.3f\n" % (jstat["time_prep"],
+                                                     jstat["time_solve"]))
+    jstat["element_stats"] = solver.element_stats() \
+        if solver.b.has("anm_element_stats") else {}
+    jstat["order"] = hyper.order
+    jstat["name"] = name
+    jstat["pade"] = bool(hyper.use_pade)
+    jstat["iter"] = log.total_nr_iter - iter_begin
+
+    out_mesh = make_out_mesh(xt)
+    jstat["force_rms_recomp"] = DeformableBody.compute_force_rms(
+        model, xt, f_load_sub, out_mesh, True)
+    jstat["mesh_V"] = deformable.mesh.nr_vertices
+    jstat["mesh_F"] = deformable.mesh.nr_faces
+    jstat["displacement"] = relative_displacement(deformable.mesh.vertices,
+                                                  out_mesh.vertices)
+    jstat["nr_inverted"] = get_nr_inverted(deformable.mesh.tets,
+                                           deformable.mesh.vertices,
+                                           out_mesh.vertices)
+    if save:
+        out = config["out_filename"]
+        deformable.mesh.write_obj(out + "-orig.obj")
+        out += "-i%d-%s" % (inverse_mode, energy)
+        out_mesh.write_obj(out + ".obj")
+        with open(out + ".json", "w") as f:
+            json.dump(jstat, f, indent=4)
+    return out_mesh, jstat
+
+
+def run_with_vtx_delta(name: str, config: dict, deformable: DeformableBody,
+                       vtx_delta: np.ndarray, vtx_coord: np.ndarray,
+                       require_refine: bool,
+                       refine_f_load: Optional[np.ndarray] = None,
+                       log: Optional[RunLog] = None) -> dict:
+    """fea/main.cpp:436-582; ``vtx_coord`` is updated in place"""
+    log = log or RunLog()
+    log.say("solving %s(delta) " % name)
+    jstat: dict = {}
+    b = deformable.b
+    vtx_dst_boundary = deformable.mesh.vertices + vtx_delta
+    energy = config["energy_model"]
+    t_acc = 0.0
+    t0 = time.perf_counter()
+    model = deformable.make_forward(energy, vtx_coord, vtx_delta)
+
+    def eval_force_rms():
+        m = deformable.make_forward(energy, vtx_coord)
+        force = m.lt_out.apply(m.graph.eval_unary_func(
+            m.y, m.lt_inp.desc.apply(m.lt_inp.x0)))
+        return norm_rms(force)
+
+    def eval_potential():
+        m = deformable.make_forward(energy, vtx_coord)
+        if m.potential is None:
+            return -1.0
+        e = m.graph.eval_unary_func(m.potential,
+                                    m.lt_inp.desc.apply(m.lt_inp.x0))
+        return float(e.sum())
+
+    iter_begin = log.total_nr_iter
+    time_prep = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    hyper = setup_solver_param(config, solution_check_tol=10.0)
+    log.say("order=%d:" % hyper.order)
+    solver = ANMImplicitSolver(model.y, model.lt_inp.desc, model.lt_out,
+                               model.lt_inp.x0, 0.0, hyper)
+    xt = run_anm_implicit(solver, log, 1.0)
+    t_acc += time.perf_counter() - t0
+    jstat["element_stats"] = [solver.element_stats()] \
+        if b.has("anm_element_stats") else []
+    log.say("timing(sec): prep=%.3f solve=%.3f\n" % (time_prep, t_acc))
+    replace_with_mask(vtx_coord, deformable.coord_fixed_mask, xt)
+    vtx_coord += vtx_delta
+    force_rms = eval_force_rms()
+    log.say("force rms: %g\n" % force_rms)
+    require_refine = require_refine or force_rms >= RMS_THRESH_FORCE_EQU
+    iter_before_refine = log.total_nr_iter
+    if require_refine:
+        m2 = deformable.make_forward(energy, vtx_coord)
+        if refine_f_load is not None:
+            f_load_sub = m2.lt_inp.copy_vtx_values(refine_f_load)
+        else:
+            f_load_sub = np.zeros_like(m2.lt_inp.x0)
+        hyper2 = setup_solver_param(config, converge_rms=RMS_THRESH_FORCE_EQU)
+        hyper2.order = 6  # fea/main.cpp:565
+        t0 = time.perf_counter()
+        solver2 = ANMEqnSolver(m2.y, m2.lt_inp.desc, m2.lt_out, m2.lt_inp.x0,
+                               f_load_sub, hyper2)
+        log.say("refine %s:" % name)
+        xt2 = run_anm_eqn(solver2, log)
+        t_acc += time.perf_counter() - t0
+        if b.has("anm_element_stats"):
+            jstat["element_stats"].append(solver2.element_stats())
+        replace_with_mask(vtx_coord, deformable.coord_fixed_mask, xt2)
+    # postprocess: enforce the boundary, recompute diagnostics
+    vtx_coord[deformable.coord_fixed_mask] = \
+        vtx_dst_boundary[deformable.coord_fixed_mask]
+    jstat["force_rms_recomp"] = eval_force_rms()
+    jstat["potential_recomp"] = eval_potential()
+    m = deformable.mesh
+    jstat["displacement"] = relative_displacement(m.vertices, vtx_coord)
+    jstat["nr_inverted"] = get_nr_inverted(m.tets, m.vertices, vtx_coord)
+    jstat["V"] = m.nr_vertices
+    jstat["F"] = m.nr_faces
+    jstat["iter_tot"] = log.total_nr_iter - iter_begin
+    jstat["iter_deform"] = iter_before_refine - iter_begin
+    jstat["iter_refine"] = log.total_nr_iter - iter_before_refine
+    jstat["time"] = t_acc
+    jstat["pade"] = bool(hyper.use_pade)
+    return jstat
+
+
+def lumped_gravity(mesh: TetrahedralMesh, density: float, g_acc: np.ndarray):
+    """fea/main.cpp:1027-1037: a quarter of each tet's weight on its nodes"""
+    grav = mesh.tet_volumes[:, None] * density * g_acc[None, :]   # [N, 3]
+    f = np.zeros((mesh.nr_vertices, 3))
+    for j in range(4):
+        np.add.at(f, mesh.tets[:, j], grav / 4)
+    return f, float(np.linalg.norm(grav, axis=1).sum())
+
+
+def setup_boundary_by_config(deformable: DeformableBody,
+                             default_proj_dir: np.ndarray, config: dict,
+                             log: RunLog):
+    """fea/main.cpp:921-982: fix the surface vertices with the lowest
+    projection along a direction"""
+    mesh = deformable.mesh
+    vtx = mesh.vertices
+    proj_dir = np.asarray(config.get("boundary_proj_dir", default_proj_dir),
+                          dtype=np.float64)
+    proj_dir = proj_dir / np.linalg.norm(proj_dir)
+    p = vtx @ proj_dir
+    thresh = p.min() + (p.max() - p.min()) * float(config["boundary_thresh"])
+    log.say("proj range: %g %g thr=%g\n" % (p.min(), p.max(), thresh))
+    sel = p <= thresh
+    if "boundary_filter" in config:
+        fcfg = config["boundary_filter"]
+        d = np.asarray(fcfg["dir"], dtype=np.float64)
+        q = vtx @ d
+        span = q.max() - q.min()
+        th0 = q.min() + span * float(fcfg["min"])
+        th1 = q.min() + span * float(fcfg["max"])
+        sel &= (q >= th0) & (q <= th1)
+    assert len(mesh.surface_vtx)
+    on_surface = np.zeros(mesh.nr_vertices, bool)
+    on_surface[mesh.surface_vtx] = True
+    deformable.coord_fixed_mask[sel & on_surface] = True
+
+
+def task_gravity(b: Binding, rootpath: str, config: dict, save=True,
+                 log: Optional[RunLog] = None):
+    """fea/main.cpp:984-1046"""
+    log = log or RunLog()
+    material = make_material_property(config["material"], True)
+    mesh_file = os.path.join(rootpath, config["mesh"])
+    mesh = TetrahedralMesh.from_tetgen_files(mesh_file)
+    deformable = DeformableBody(b, material, mesh)
+    g_acc = np.asarray(config["g"], dtype=np.float64)
+    if "scale" in config:
+        mesh.resize_inplace(float(config["scale"]))
+    if os.path.exists(mesh_file + ".bou"):
+        with open(mesh_file + ".bou") as f:
+            ids = np.array(f.read().split(), dtype=np.int64)
+        assert (ids > 0).all()
+        deformable.coord_fixed_mask[ids - 1] = True
+    else:
+        log.say("bou file does not exist; fix lowest points ...\n")
+        setup_boundary_by_config(deformable, -g_acc, config, log)
+    if save:
+        mesh.write_obj(config["out_filename"] + "-boundary.obj",
+                       np.nonzero(deformable.coord_fixed_mask[:, 0])[0])
+    f_load_full, tot = lumped_gravity(mesh, material.density, g_acc)
+    log.say("mesh loading finished %s:\n nr_vtx=%d nr_tet=%d boundary_vtx=%d "
+            "gravity=%.3f\n" % (mesh_file, mesh.nr_vertices, mesh.nr_tet,
+                                int(deformable.coord_fixed_mask[:, 0].sum()),
+                                tot))
+    return run_and_save("mesh %s" % os.path.basename(mesh_file), config,
+                        deformable, bool(config.get("inverse", False)),
+                        f_load_full, save, log)
+
+
+def task_test_cuboid(b: Binding, config: dict, save=True,
+                     log: Optional[RunLog] = None):
+    """fea/main.cpp:623-663"""
+    log = log or RunLog()
+    nx, ny, nz = int(config["x"]), int(config["y"]), int(config["z"])
+    spacing = float(config["spacing"])
+    material = make_material_property(config["material"])
+    deformable = DeformableBody(
+        b, material, TetrahedralMesh.make_cuboid(nx, ny, nz, spacing))
+    vtx = deformable.mesh.vertices
+    deformable.coord_fixed_mask[vtx[:, 0] <= spacing / 2.0] = True
+    f_load_full = np.zeros_like(vtx)
+    sel = ((vtx[:, 0] > (nx // 2 - 1) * spacing - spacing / 2.0) &
+           (vtx[:, 2] < spacing / 2.0))
+    f_load_full[sel, 2] = -50.0
+    inverse = bool(config.get("inverse", False))
+    return run_and_save("cuboid inverse" if inverse else "cuboid", config,
+                        deformable, inverse, f_load_full, save, log)
+
+
+def task_test_cuboid_twist(b: Binding, config: dict, save=True,
+                           log: Optional[RunLog] = None):
+    """fea/main.cpp:665-772; returns (final vertices, stats of every stage)"""
+    log = log or RunLog()
+    config = dict(config)
+    nx, ny, nz = int(config["x"]), int(config["y"]), int(config["z"])
+    spacing = float(config["spacing"])
+    material = make_material_property(config["material"])
+    mesh = TetrahedralMesh.make_cuboid(nx, ny, nz, spacing)
+    log.say("cuboid twist: V=%d F=%d\n" % (mesh.nr_vertices, mesh.nr_faces))
+    deformable = DeformableBody(b, material, mesh)
+    x_thresh = spacing * (nx - 1.5)
+    vtx_cur = mesh.vertices.copy()
+    left = vtx_cur[:, 0] <= spacing / 2.0
+    right = vtx_cur[:, 0] >= x_thresh
+    deformable.coord_fixed_mask[left | right] = True
+    bnd = np.nonzero(right)[0]
+    assert len(bnd)
+    out_filename = config["out_filename"]
+    stats: List[dict] = []
+    save_cnt = [0]
+
+    def do_save():
+        if save:
+            mesh.write_obj("%s-%d.obj" % (out_filename, save_cnt[0]),
+                           vertices=vtx_cur)
+        save_cnt[0] += 1
+
+    def update_to_next(name, bnd_next, require_refine):
+        vtx_delta = np.zeros_like(vtx_cur)
+        vtx_delta[bnd] = bnd_next - vtx_cur[bnd]
+        st = run_with_vtx_delta(name, config, deformable, vtx_delta, vtx_cur,
+                                require_refine, None, log)
+        st["name"] = name
+        stats.append(st)
+        do_save()
+
+    save_interm = bool(config.get("save_interm", False))
+    config["save_interm"] = False
+    rotate_split = float(config.get("rotate_split", 90))
+    remain = float(config["rotate"])
+    finished = 0.0
+    do_save()
+    bnd_init = vtx_cur[bnd].copy()
+    quadrant = 0
+    while remain > 1e-5:
+        rot = min(remain, rotate_split)
+        remain -= rot
+        finished += rot
+        a = finished * math.pi / 180
+        rmat = np.array([[1, 0, 0], [0, math.cos(a), -math.sin(a)],
+                         [0, math.sin(a), math.cos(a)]])
+        nxt = bnd_init @ rmat.T
+        nxt = nxt + (bnd_init.mean(axis=0) - nxt.mean(axis=0))[None, :]
+        update_to_next("rot%d(rem %.1f)" % (quadrant, remain), nxt, False)
+        quadrant += 1
+    bnd_init = vtx_cur[bnd].copy()
+    config["save_interm"] = save_interm
+    for bend in config.get("bend", []):
+        a = float(bend["angle"]) * math.pi / 180
+        shift = np.asarray(bend["shift"], dtype=np.float64)
+        rmat = np.array([[math.cos(a), -math.sin(a), 0],
+                         [math.sin(a), math.cos(a), 0], [0, 0, 1]])
+        nxt = bnd_init @ rmat.T + (shift * spacing)[None, :]
+        update_to_next("bend", nxt, True)
+    if save and stats:
+        last = dict(stats[-1])
+        last["V"], last["F"] = mesh.nr_vertices, mesh.nr_faces
+        with open(out_filename + ".json", "w") as f:
+            json.dump(last, f, indent=4)
+    return vtx_cur, stats
+
+
+def task_mesh_twist(b: Binding, rootpath: str, config: dict, save=True,
+                    log: Optional[RunLog] = None):
+    """fea/main.cpp:774-919; returns (final vertices, stats)"""
+    log = log or RunLog()
+    material = make_material_property(config["material"])
+    mesh_file = os.path.join(rootpath, config["mesh"])
+    mesh = TetrahedralMesh.from_tetgen_files(mesh_file)
+    s = float(config.get("scale", 0))
+    if s > 0:
+        mesh.resize_inplace(s)
+    log.say("mesh twist: V=%d F=%d\n" % (mesh.nr_vertices, mesh.nr_faces))
+    deformable = DeformableBody(b, material, mesh)
+    axis = np.asarray(config["axis"], dtype=np.float64)
+    out_filename = config["out_filename"]
+    p = mesh.vertices @ axis
+    proj_min, proj_max = p.min(), p.max()
+    proj_dist = proj_max - proj_min
+    thresh0 = proj_min + proj_dist * float(config["ratio_lo"])
+    thresh1 = proj_min + proj_dist * (1 - float(config["ratio_hi"]))
+    log.say("proj range: %g %g thr=%g,%g\n" % (proj_min, proj_max, thresh0,
+                                               thresh1))
+    assert len(mesh.surface_vtx)
+    cand = np.ones(mesh.nr_vertices, bool)
+    if not config.get("include_int_points", False):
+        cand[:] = False
+        cand[mesh.surface_vtx] = True
+    fixed = ((p <= thresh0) | (p >= thresh1)) & cand
+    deformable.coord_fixed_mask[fixed] = True
+    bnd = np.nonzero(fixed & (p >= thresh1))[0]
+    fixed_vid = np.nonzero(fixed)[0]
+    if save:
+        mesh.write_obj(out_filename + "-orig.obj")
+        mesh.write_obj(out_filename + "-boundary.obj", fixed_vid)
+    f_load_full = None
+    if config.get("add_gravity", False):
+        g_acc = np.asarray(config["g"], dtype=np.float64)
+        f_load_full, tot = lumped_gravity(mesh, material.density, g_acc)
+        log.say("add gravity=%.3f\n" % tot)
+        cfg2 = dict(config)
+        cfg2["save_interm"] = False
+        deformed, _ = run_and_save("gravity_init", cfg2, deformable, False,
+                                   f_load_full, False, log)
+        vtx_cur = deformed.vertices.copy()
+    else:
+        vtx_cur = mesh.vertices.copy()
+    bnd_next = vtx_cur[bnd].copy()
+
+    def apply_trans(cfg, bnd_next):
+        angle = float(cfg["angle"]) * math.pi / 180
+        shift = np.asarray(cfg["shift"], dtype=np.float64)
+        rot_axis = int(cfg.get("rot_axis", 2))
+        small = np.array([[math.cos(angle), -math.sin(angle)],
+                          [math.sin(angle), math.cos(angle)]])
+        rmat = np.eye(3)
+        for i in range(3):
+            for j in range(3):
+                if i != rot_axis and j != rot_axis:
+                    rmat[i, j] = small[i - (i > rot_axis), j - (j > rot_axis)]
+        return bnd_next @ rmat.T + (shift * proj_dist)[None, :]
+
+    if "transforms" in config:
+        for tcfg in config["transforms"]:
+            bnd_next = apply_trans(tcfg, bnd_next)
+    else:
+        bnd_next = apply_trans(config, bnd_next)
+    vtx_delta = np.zeros_like(vtx_cur)
+    vtx_delta[bnd] = bnd_next - vtx_cur[bnd]
+    if save:
+        mesh.write_obj(out_filename + "-boundary-dst.obj", fixed_vid,
+                       vertices=vtx_cur + vtx_delta)
+    stat = run_with_vtx_delta("mesh_twist", config, deformable, vtx_delta,
+                              vtx_cur, False, f_load_full, log)
+    mesh.replace_vtx(vtx_cur)
+    if save:
+        mesh.write_obj(out_filename + ".obj")
+        with open(out_filename + ".json", "w") as f:
+            json.dump(stat, f, indent=4)
+    return vtx_cur, stat
+
+
+def load_config(task_json: str, overrides=()) -> dict:
+    """fea/main.cpp:1075-1079: json::update merges top-level keys"""
+    with open(task_json) as f:
+        config = json.load(f)
+    for o in overrides:
+        with open(o) as f:
+            config.update(json.load(f))
+    return config
+
+
+def run_task(b: Binding, task_json: str, overrides=(), save=True,
+             log: Optional[RunLog] = None, config: Optional[dict] = None):
+    """dispatch on ``func`` like fea/main.cpp:1080-1101"""
+    if config is None:
+        config = load_config(task_json, overrides)
+    root = os.path.dirname(os.path.abspath(task_json))
+    func = config["func"]
+    if func == "gravity":
+        return task_gravity(b, root, config, save, log)
+    if func == "mesh_twist":
+        return task_mesh_twist(b, root, config, save, log)
+    if func == "test_cuboid":
+        return task_test_cuboid(b, config, save, log)
+    if func == "test_cuboid_twist":
+        return task_test_cuboid_twist(b, config, save, log)
+    raise RuntimeError(f"unknown func: {func}")
+
+
+def main(argv=None) -> int:
+    argv = sys.argv if argv is None else argv
+    if len(argv) < 3:
+        sys.stderr.write("usage: %s <system config file> <task config file> "
+                         "[<task override json files ...>]\n" % argv[0])
+        return -1
+    import sanm_b200
+    with open(argv[1]) as f:
+        sysconf = json.load(f)
+    b = sanm_b200.load()
+    if "gpu" in sysconf:
+        b.call("set_device", int(sysconf["gpu"]))
+    try:
+        run_task(b, argv[2], argv[3:])
+    except Exception as e:  # fea/main.cpp:1104-1111
+        sys.stderr.write("error: %s\n" % e)
+        return 2
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
