@@ -301,7 +301,13 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     b = sanm_b200.load()
     b.call("set_device", ctypes.c_int(local_rank))
-    stream = torch.cuda.current_stream()
+    # a dedicated (non-default) stream shared by torch's events and the
+    # library's kernels: handle 0 (the legacy default stream) means "library's
+    # own stream" to sanm_set_stream, and events recorded there would not see
+    # the kernels
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     b.call("set_stream", ctypes.c_void_p(stream.cuda_stream))
 
     def barrier():

@@ -504,9 +504,36 @@ void AnmSolver::solve_expansion_coeffs() {
                                  m_kind == IMPLICIT ? m_d_grad_t.ptr() : nullptr,
                                  m_prop->ensure_jacobian());
             }
+            static const bool dbg = getenv("SANM_DEBUG_FINITE") != nullptr;
+            if (dbg) {
+                auto chk = [&](const char* nm, const double* p, size_t cnt) {
+                    std::vector<double> h(cnt);
+                    rt::d2h(h.data(), p, cnt * sizeof(double));
+                    size_t bad = 0, first = 0;
+                    double mx = 0;
+                    for (size_t q = 0; q < cnt; ++q) {
+                        if (!std::isfinite(h[q])) {
+                            if (!bad) first = q;
+                            ++bad;
+                        } else mx = std::max(mx, std::fabs(h[q]));
+                    }
+                    printf("[dbg] %s: n=%zu bad=%zu first=%zu max=%g\n", nm, cnt, bad, first, mx);
+                };
+                chk("kvals", m_d_kvals.ptr(), m_kasm->nnz());
+                chk("grad_t", grad_t, n);
+                chk("jac", m_prop->ensure_jacobian(), m_prop->batch() * m_prop->out_elems() * (m_prop->jacobian_type() == TaylorProp::JAC_ELEMWISE ? 1 : m_prop->in_elems()));
+                chk("fx", m_d_fx.ptr(), n);
+            }
             {
                 SANM_PROF("sparse_prep");
                 m_lu.factor(m_d_kvals.ptr());
+            }
+            if (dbg) {
+                std::vector<double> h(n);
+                m_lu.solve(m_d_tmp.ptr(), grad_t);
+                rt::d2h(h.data(), m_d_tmp.ptr(), n * sizeof(double));
+                size_t bad = 0; for (double v : h) bad += !std::isfinite(v);
+                printf("[dbg] xgt bad=%zu\n", bad); fflush(stdout);
             }
             {
                 SANM_PROF("sparse_solve");

@@ -668,8 +668,13 @@ def run_with_vtx_delta(name: str, config: dict, deformable: DeformableBody,
             jstat["element_stats"].append(solver2.element_stats())
         replace_with_mask(vtx_coord, deformable.coord_fixed_mask, xt2)
     # postprocess: enforce the boundary, recompute diagnostics
-    vtx_coord[deformable.coord_fixed_mask] = \
-        vtx_dst_boundary[deformable.coord_fixed_mask]
+    # fea/main.cpp:452-461 iterates `j < mask.rows()` over a 3 x V mask, so
+    # the reference only ever touches vertices 0..2 here; kept as is, because
+    # the chained stages of test_cuboid_twist depend on it (vtx_dst_boundary
+    # is rest + delta, which is not the target once vtx_coord has moved)
+    for j in range(min(3, len(vtx_coord))):
+        m = deformable.coord_fixed_mask[j]
+        vtx_coord[j][m] = vtx_dst_boundary[j][m]
     jstat["force_rms_recomp"] = eval_force_rms()
     jstat["potential_recomp"] = eval_potential()
     m = deformable.mesh
