@@ -345,7 +345,8 @@ def run_ours(args):
     launches = b.launch_count() - launches0
     prof = {t: b.prof_get(t) for t in
             ("taylor_next_order", "push_xi", "remap_out", "k_order_bias",
-             "k_order_coef", "k_order_eval", "k_jacobian")}
+             "k_order_coef", "k_order_eval", "k_jacobian", "k_fused_eval",
+             "k_fused_step", "k_fused_jacobian")}
     clocks = sampler.stop()
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region

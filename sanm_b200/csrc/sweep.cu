@@ -70,15 +70,7 @@ public:
     }
 
     //! doubles of Taylor state per item and order that later orders re-read
-    int state_doubles() const {
-        int s = 0;
-        const Lowered& L = m_prop->lowered();
-        for (auto& v : L.vars) {
-            if (v.needs_stack && !v.is_const) s += v.e;
-        }
-        for (auto& o : L.ops) s += o.eauxk;
-        return s;
-    }
+    int state_doubles() const { return m_prop->state_doubles(); }
 
     double steps() const { return (double)m_prop->batch() * m_order; }
 

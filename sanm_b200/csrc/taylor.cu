@@ -91,6 +91,17 @@ void TaylorProp::reset() {
     m_xi_known = false;
     m_jac_done = false;
     if (m_flags.size()) m_flags.zero();
+    if (m_fused) m_fused->reset();
+}
+
+int TaylorProp::state_doubles() const {
+    if (m_fused) return m_fused->state_doubles();
+    int s = 0;
+    for (auto& v : m_low.vars) {
+        if (v.needs_stack && !v.is_const) s += v.e;
+    }
+    for (auto& o : m_low.ops) s += o.eauxk;
+    return s;
 }
 
 void TaylorProp::prepare(const Shape& x_shape) {
@@ -101,6 +112,18 @@ void TaylorProp::prepare(const Shape& x_shape) {
     }
     m_low = lower_graph(*m_graph, m_out_var, x_shape);
     const uint64_t n = m_low.batch;
+    m_fused.reset();
+    {
+        FusedSpec spec = match_fea_graph(*m_graph, m_out_var, x_shape);
+        if (spec.material != fused::MAT_NONE) {
+            m_fused.reset(new FusedProp{*m_graph, spec, n, m_max_order});
+            m_npad = m_fused->npad();
+            m_arena.release();
+            m_prepared = true;
+            reset();
+            return;
+        }
+    }
     m_npad = (int64_t)((n + 31) / 32 * 32);
     const int K = m_max_order;
 
@@ -241,11 +264,13 @@ void TaylorProp::prepare(const Shape& x_shape) {
 
 double* TaylorProp::input_slot(int k) const {
     sanm_check(m_prepared && k >= 0 && k <= m_max_order);
+    if (m_fused) return m_fused->ds_slot();
     return vbase(m_hvars[m_low.input], k);
 }
 
 const double* TaylorProp::output_slot(int k) const {
     sanm_check(m_prepared && k >= 0 && k <= m_max_order);
+    if (m_fused) return m_fused->out_slot();
     return vbase(m_hvars[m_low.output], k);
 }
 
@@ -259,6 +284,12 @@ void TaylorProp::launch(int k, int phase, int sb_zero) {
 void TaylorProp::push_xi_filled() {
     // libsanm/symbolic.cpp:162-204
     sanm_check(m_prepared && !m_xi_known, "push_xi called twice in a row");
+    if (m_fused) {
+        if (m_order < 0) m_order = 0;
+        m_fused->push(m_order);
+        m_xi_known = true;
+        return;
+    }
     if (m_order < 0) {
         m_order = 0;
         launch(0, PH_EVAL, 0);
@@ -275,6 +306,13 @@ void TaylorProp::compute_next_order_bias() {
                "compute_next_order_bias needs a preceding push_xi");
     sanm_check(m_order + 1 <= m_max_order, "order %d exceeds max_order %d",
                m_order + 1, m_max_order);
+    if (m_fused) {
+        // the Jacobian depends on the order-0 slot only: computed on demand
+        ++m_order;
+        m_xi_known = false;
+        m_fused->next_bias(m_order);
+        return;
+    }
     ensure_jacobian();
     ++m_order;
     m_xi_known = false;
@@ -291,6 +329,13 @@ void TaylorProp::compute_next_order_bias() {
 
 const double* TaylorProp::ensure_jacobian() {
     if (m_jac_done) return m_jac.ptr();
+    if (m_fused) {
+        sanm_check(m_order >= 0, "Jacobian needs the order-0 point");
+        m_jac.ensure(m_low.batch * 81);
+        m_fused->jacobian(m_jac.ptr());
+        m_jac_done = true;
+        return m_jac.ptr();
+    }
     sanm_check(m_order == 0 && m_xi_known,
                "Jacobian must be requested right after the first push_xi");
     const uint64_t n = m_low.batch;
@@ -344,7 +389,7 @@ void TaylorProp::output_to_host(int k, double* out) const {
 void TaylorProp::check_device_error() {
     if (!m_prepared) return;
     int err = 0;
-    rt::d2h(&err, m_flags.ptr(), sizeof(int));
+    rt::d2h(&err, m_fused ? m_fused->err_flag() : m_flags.ptr(), sizeof(int));
     if (err & 1) {
         sanm_throw(SANM_ERR_NUMERICAL, "0^p when p is not integer");
     }

@@ -4,6 +4,7 @@
  */
 #pragma once
 
+#include "fused.h"
 #include "graph.h"
 
 namespace sanm_b200 {
@@ -68,7 +69,13 @@ public:
     //! synchronises the stream
     void check_device_error();
 
-    uint64_t arena_bytes() const { return m_arena.size() * sizeof(double); }
+    uint64_t arena_bytes() const {
+        return m_fused ? m_fused->arena_bytes() : m_arena.size() * sizeof(double);
+    }
+    //! true when the graph runs on the fused element kernels (fused.h)
+    bool is_fused() const { return (bool)m_fused; }
+    //! doubles of Taylor state per item and order that later orders re-read
+    int state_doubles() const;
 
 private:
     std::shared_ptr<const Graph> m_graph;
@@ -85,6 +92,7 @@ private:
     std::vector<taylor::DVar> m_hvars;
     std::vector<taylor::DOp> m_hops;
     taylor::DProgram m_prog{};
+    std::unique_ptr<FusedProp> m_fused;
 
     void launch(int k, int phase, int sb_zero);
 };

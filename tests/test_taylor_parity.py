@@ -72,9 +72,14 @@ def make_F_coeffs(rng, n, order, scale=0.5, amp=0.02):
 MATERIAL = mat.MaterialProperty.from_young_poisson(1e6, 0.45)
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("energy", [mat.NEOHOOKEAN_I, mat.NEOHOOKEAN_C,
                                     mat.ARAP, mat.STVK_STRETCH])
-def test_pk1_graphs(impl, ref, energy):
+def test_pk1_graphs(impl, ref, energy, fused, monkeypatch):
+    """fused=True: the register-resident element kernels (csrc/fused_dev.h)
+    take the three fea graphs; fused=False: the same graphs through the generic
+    operator-list kernels (csrc/taylor_dev.h).  stvk_stretch is always generic."""
+    monkeypatch.setenv("SANM_NO_FUSED", "0" if fused else "1")
     rng = np.random.default_rng(92702102)
     n, order = 37, 20
     xs = make_F_coeffs(rng, n, order)
