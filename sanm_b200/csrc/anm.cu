@@ -457,18 +457,23 @@ void AnmSolver::solve_expansion_coeffs() {
     m_nr_coeffs = 1;
 
     const Shape elem_shape = m_rin->out_shape();
-    {
-        SANM_PROF("push_xi");
-        m_prop->prepare(elem_shape);
-        const VecLayout soa_in{m_prop->in_elems(), m_prop->npad()};
-        m_rin->apply(m_prop->input_slot(0), soa_in, m_d_xt.ptr(), VecLayout{});
-        m_prop->push_xi_filled();
-    }
-    const VecLayout soa_in{m_prop->in_elems(), m_prop->npad()};
-    const VecLayout soa_out{m_prop->out_elems(), m_prop->npad()};
+    m_prop->prepare(elem_shape);
     sanm_check(m_rout->nr_in() == m_prop->batch() * m_prop->out_elems(),
                "remap_out input size does not match the function output");
-    {
+    // fused I/O: gather and assembly happen inside the element kernels
+    const bool fio = m_prop->attach_io(*m_rin, *m_rout);
+    const VecLayout soa_in{m_prop->in_elems(), m_prop->npad()};
+    const VecLayout soa_out{m_prop->out_elems(), m_prop->npad()};
+    if (fio) {
+        SANM_PROF("push_xi");
+        m_prop->push_xi_from(m_d_xt.ptr(), m_d_fx.ptr());
+    } else {
+        {
+            SANM_PROF("push_xi");
+            m_rin->apply(m_prop->input_slot(0), soa_in, m_d_xt.ptr(),
+                         VecLayout{});
+            m_prop->push_xi_filled();
+        }
         SANM_PROF("remap_out");
         m_rout->apply(m_d_fx.ptr(), VecLayout{}, m_prop->output_slot(0), soa_out);
     }
@@ -484,7 +489,11 @@ void AnmSolver::solve_expansion_coeffs() {
         double* xti = m_d_xt.ptr() + (size_t)i * m_ld;
         {
             SANM_PROF("taylor_next_order");
-            m_prop->compute_next_order_bias();
+            if (fio) {
+                m_prop->compute_next_order_bias_to(m_d_bi.ptr());
+            } else {
+                m_prop->compute_next_order_bias();
+            }
         }
         if (i == 1) {
             // the first-order bias is zero (libsanm/anm.cpp:236); build and
@@ -544,7 +553,7 @@ void AnmSolver::solve_expansion_coeffs() {
             rt::for_each(n + 1, CombineX{xti, m_d_xgt.ptr(), nullptr, sc, n});
             dot_to(SC_XGT_X1, x1, m_d_xgt.ptr(), n);
         } else {
-            {
+            if (!fio) {
                 SANM_PROF("remap_out");
                 m_rout->apply(m_d_bi.ptr(), VecLayout{}, m_prop->output_slot(i),
                               soa_out);
@@ -574,8 +583,12 @@ void AnmSolver::solve_expansion_coeffs() {
         }
         if (i < K) {
             SANM_PROF("push_xi");
-            m_rin->apply(m_prop->input_slot(i), soa_in, xti, VecLayout{});
-            m_prop->push_xi_filled();
+            if (fio) {
+                m_prop->push_xi_from(xti);
+            } else {
+                m_rin->apply(m_prop->input_slot(i), soa_in, xti, VecLayout{});
+                m_prop->push_xi_filled();
+            }
         }
     }
     m_stats.tet_order_steps += (double)m_prop->batch() * K;

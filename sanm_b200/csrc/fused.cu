@@ -18,6 +18,7 @@ struct KArgs {
     const double* xbias;
     int* err;
     int64_t npad;
+    uint64_t n;
     int K1;
     Params pr;
 };
@@ -47,43 +48,140 @@ SANM_HD inline void st_soa(double* base, const double* src, int64_t np,
     for (int c = 0; c < N; ++c) base[(int64_t)c * np + t] = src[c];
 }
 
-template <class M>
+//! device view of FusedIO (fused_io.h) plus the nodal vectors of one launch
+struct IOArgs {
+    const uint32_t* uidx;
+    const uint32_t* gidx;
+    const double* gcoef;
+    int wu;
+    const double* nrm;
+    const uint16_t* lrow;
+    const uint32_t* blk_ptr;
+    const uint32_t* con_ptr;
+    const uint16_t* con_idx;
+    double* partial;
+    const double* x;  //!< nodal coefficient being pushed
+};
+
+//! Ds = remap_in(x) for one tet (fea/mesh_template.h:73-110)
+template <bool IO>
+SANM_HD inline void load_ds(double* Ds, const KArgs& a, const IOArgs& io,
+                            size_t t) {
+    if (!IO) {
+        ld_soa<9>(Ds, a.ds, a.npad, t);
+        return;
+    }
+#pragma unroll
+    for (int q = 0; q < 9; ++q) {
+        double s = 0;
+        for (int w = 0; w < io.wu; ++w) {
+            const uint32_t u = io.uidx[((int64_t)w * 9 + q) * a.npad + t];
+            if (u != 0xFFFFFFFFu) {
+                const double v = io.x[u >> 1];
+                s += (u & 1) ? -v : v;
+            }
+        }
+        if (io.gidx) {
+            const uint32_t g = io.gidx[(int64_t)q * a.npad + t];
+            if (g != 0xFFFFFFFFu) s += io.x[g] * io.gcoef[(int64_t)q * a.npad + t];
+        }
+        Ds[q] = s;
+    }
+}
+
+//! the 12 nodal contributions P n_d of one tet into shared memory
+//! (fea/mesh_template.h:145-160)
+SANM_HD inline void emit_forces(double* vals, int lane, const double* P,
+                                const KArgs& a, const IOArgs& io, size_t t) {
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        const double n0 = io.nrm[((int64_t)d * 3 + 0) * a.npad + t];
+        const double n1 = io.nrm[((int64_t)d * 3 + 1) * a.npad + t];
+        const double n2 = io.nrm[((int64_t)d * 3 + 2) * a.npad + t];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            vals[(d * 3 + c) * TILE + lane] =
+                    n0 * P[c * 3] + n1 * P[c * 3 + 1] + n2 * P[c * 3 + 2];
+        }
+    }
+}
+
+//! first level of the assembly: one partial sum per distinct row of the block
+SANM_HD inline void block_reduce(const rt::BlockCtx& c, const double* vals,
+                                 const IOArgs& io) {
+    const uint32_t base = io.blk_ptr[c.bid], end = io.blk_ptr[c.bid + 1];
+    for (uint32_t g = base + c.tid; g < end; g += c.nthr) {
+        double s = 0;
+        for (uint32_t p = io.con_ptr[g], pe = io.con_ptr[g + 1]; p < pe; ++p) {
+            s += vals[io.con_idx[p]];
+        }
+        io.partial[g] = s;
+    }
+}
+
+template <class M, bool IO>
 struct Eval0Kernel {
     KArgs a;
-    SANM_D void operator()(size_t t) const {
-        double Ds[9], dm[9], F0[9], s0[M::S], aux[M::AUX ? M::AUX : 1], P0[9];
-        ld_soa<9>(Ds, a.ds, a.npad, t);
-        if (a.xbias) {
-            double xb[9];
-            ld_soa<9>(xb, a.xbias, a.npad, t);
+    IOArgs io;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        double* vals = reinterpret_cast<double*>(c.smem);
+        for (int lane = c.tid; lane < TILE; lane += c.nthr) {
+            const size_t t = c.bid * TILE + lane;
+            if (t >= a.n) continue;
+            double Ds[9], dm[9], F0[9], s0[M::S], aux[M::AUX ? M::AUX : 1],
+                    P0[9];
+            load_ds<IO>(Ds, a, io, t);
+            if (a.xbias) {
+                double xb[9];
+                ld_soa<9>(xb, a.xbias, a.npad, t);
 #pragma unroll
-            for (int q = 0; q < 9; ++q) Ds[q] += xb[q];
+                for (int q = 0; q < 9; ++q) Ds[q] += xb[q];
+            }
+            ld_soa<9>(dm, a.dminv, a.npad, t);
+            taylor::mm3(F0, Ds, dm);
+            M::eval0(F0, s0, aux, P0, a.pr, a.err);
+            st_strided<M::S>(slot_ptr<M>(a, t, 0), s0);
+            if (M::AUX) st_strided<M::AUX>(aux_ptr<M>(a, t), aux);
+            st_soa<9>(a.out, P0, a.npad, t);
+            if (IO) emit_forces(vals, lane, P0, a, io, t);
         }
-        ld_soa<9>(dm, a.dminv, a.npad, t);
-        taylor::mm3(F0, Ds, dm);
-        M::eval0(F0, s0, aux, P0, a.pr, a.err);
-        st_strided<M::S>(slot_ptr<M>(a, t, 0), s0);
-        if (M::AUX) st_strided<M::AUX>(aux_ptr<M>(a, t), aux);
-        st_soa<9>(a.out, P0, a.npad, t);
+        if (IO) {
+            c.sync();
+            block_reduce(c, vals, io);
+        }
     }
 };
 
 /*!
  * Coefficient phase of order k_push (x_k known: finish slot k) followed by the
  * bias phase of order kb (usually k_push + 1); either may be skipped (<= 0).
+ * One block owns one tile of TILE tets.
  */
-template <class M>
+template <class M, bool IO>
 struct StepKernel {
     KArgs a;
+    IOArgs io;
     int k_push, kb, want_out;
-    SANM_D void operator()(size_t t) const {
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        double* vals = reinterpret_cast<double*>(c.smem);
+        for (int lane = c.tid; lane < TILE; lane += c.nthr) {
+            const size_t t = c.bid * TILE + lane;
+            if (t < a.n) item(t, lane, vals);
+        }
+        if (IO && kb > 0) {
+            c.sync();
+            block_reduce(c, vals, io);
+        }
+    }
+
+    SANM_D void item(size_t t, int lane, double* vals) const {
         constexpr int S = M::S;
         double s0[S], aux[M::AUX ? M::AUX : 1];
         ld_strided<S>(s0, slot_ptr<M>(a, t, 0));
         if (M::AUX) ld_strided<M::AUX>(aux, aux_ptr<M>(a, t));
         if (k_push > 0) {
             double Ds[9], dm[9], sk[S], Pt[9];
-            ld_soa<9>(Ds, a.ds, a.npad, t);
+            load_ds<IO>(Ds, a, io, t);
             ld_soa<9>(dm, a.dminv, a.npad, t);
             taylor::mm3(sk, Ds, dm);  // F_k
             M::tangent(sk, s0, aux, a.pr, sk, Pt);
@@ -91,10 +189,10 @@ struct StepKernel {
             if (k_push >= 2) {
                 // bias parts were stored by the bias phase of this order
 #pragma unroll
-                for (int c = 9; c < S; ++c) sk[c] += pk[c * TILE];
+                for (int q = 9; q < S; ++q) sk[q] += pk[q * TILE];
             }
             st_strided<S>(pk, sk);
-            if (want_out) {
+            if (!IO && want_out) {
                 if (k_push >= 2) {
                     double Pb[9];
                     ld_soa<9>(Pb, a.out, a.npad, t);
@@ -124,8 +222,12 @@ struct StepKernel {
             M::bias(acc, s0, aux, kb, a.pr, bs, Pb);
             double* pb = slot_ptr<M>(a, t, kb);
 #pragma unroll
-            for (int c = 9; c < S; ++c) pb[c * TILE] = bs[c];
-            st_soa<9>(a.out, Pb, a.npad, t);
+            for (int q = 9; q < S; ++q) pb[q * TILE] = bs[q];
+            if (IO) {
+                emit_forces(vals, lane, Pb, a, io, t);
+            } else {
+                st_soa<9>(a.out, Pb, a.npad, t);
+            }
         }
     }
 };
@@ -207,34 +309,63 @@ FusedProp::FusedProp(const Graph& g, const FusedSpec& spec, uint64_t batch,
 
 void FusedProp::reset() {
     m_pending = -1;
+    m_pending_x = nullptr;
     m_out_is_bias = false;
     m_err.zero();
 }
 
+void FusedProp::attach_io(std::shared_ptr<const FusedIO> io) {
+    sanm_check(!io || (io->n_tets == m_n && io->npad == m_npad));
+    m_io = std::move(io);
+}
+
 template <class M>
-void FusedProp::launch_step(int k_push, int kb, bool want_out) {
-    KArgs a{m_arena.ptr(), m_aux.ptr(), m_ds.ptr(),  m_out.ptr(),
+void FusedProp::launch_step(int k_push, int kb, bool want_out, const double* x) {
+    KArgs a{m_arena.ptr(), m_aux.ptr(),   m_ds.ptr(),  m_out.ptr(),
             m_dminv.ptr(), m_xbias.ptr(), m_err.ptr(), m_npad,
-            m_K + 1,       m_params};
+            m_n,           m_K + 1,       m_params};
+    const size_t ntiles = (size_t)m_npad / TILE;
+    const bool use_io = x != nullptr;
+    IOArgs io{};
+    if (use_io) {
+        sanm_check(m_io && !want_out);
+        io = IOArgs{m_io->uidx.ptr(),    m_io->gidx.ptr(),    m_io->gcoef.ptr(),
+                    m_io->wu,            m_io->nrm.ptr(),     m_io->lrow.ptr(),
+                    m_io->blk_ptr.ptr(), m_io->con_ptr.ptr(), m_io->con_idx.ptr(),
+                    m_io->partial.ptr(), x};
+    }
+    const size_t smem = use_io ? 12 * TILE * sizeof(double) : 0;
     if (k_push == 0) {
         SANM_PROF("k_fused_eval");
-        rt::for_each(m_n, Eval0Kernel<M>{a});
+        if (use_io) {
+            rt::for_each_block(ntiles, TILE, smem, Eval0Kernel<M, true>{a, io});
+        } else {
+            rt::for_each_block(ntiles, TILE, smem, Eval0Kernel<M, false>{a, io});
+        }
     } else {
         SANM_PROF("k_fused_step");
-        rt::for_each(m_n, StepKernel<M>{a, k_push, kb, (int)want_out});
+        if (use_io) {
+            rt::for_each_block(
+                    ntiles, TILE, smem,
+                    StepKernel<M, true>{a, io, k_push, kb, (int)want_out});
+        } else {
+            rt::for_each_block(
+                    ntiles, TILE, smem,
+                    StepKernel<M, false>{a, io, k_push, kb, (int)want_out});
+        }
     }
 }
 
-void FusedProp::step(int k_push, int kb, bool want_out) {
+void FusedProp::step(int k_push, int kb, bool want_out, const double* x) {
     switch (m_mat) {
         case MAT_NHC:
-            launch_step<NHC>(k_push, kb, want_out);
+            launch_step<NHC>(k_push, kb, want_out, x);
             break;
         case MAT_NHI:
-            launch_step<NHI>(k_push, kb, want_out);
+            launch_step<NHI>(k_push, kb, want_out, x);
             break;
         default:
-            launch_step<ARAP>(k_push, kb, want_out);
+            launch_step<ARAP>(k_push, kb, want_out, x);
             break;
     }
 }
@@ -242,10 +373,26 @@ void FusedProp::step(int k_push, int kb, bool want_out) {
 void FusedProp::push(int k) {
     sanm_check(m_pending < 0 && k >= 0 && k <= m_K);
     if (k == 0) {
-        step(0, -1, true);
+        step(0, -1, true, nullptr);
         m_out_is_bias = false;
     } else {
         m_pending = k;
+        m_pending_x = nullptr;
+    }
+}
+
+void FusedProp::push_from(int k, const double* x, double* fx) {
+    sanm_check(m_io && m_pending < 0 && k >= 0 && k <= m_K);
+    if (k == 0) {
+        step(0, -1, false, x);
+        m_out_is_bias = false;
+        if (fx) {
+            SANM_PROF("k_assemble_final");
+            m_io->finalize(fx);
+        }
+    } else {
+        m_pending = k;
+        m_pending_x = x;
     }
 }
 
@@ -253,8 +400,9 @@ void FusedProp::flush() {
     if (m_pending < 0) return;
     // the output of a bare push is the full coefficient: bias (still in the
     // output buffer from the bias phase of this order) + tangent
+    sanm_check(!m_pending_x, "bare push is not available with fused I/O");
     sanm_check(m_pending == 1 || m_out_is_bias);
-    step(m_pending, -1, true);
+    step(m_pending, -1, true, nullptr);
     m_pending = -1;
     m_out_is_bias = false;
 }
@@ -271,18 +419,34 @@ void FusedProp::next_bias(int kb) {
         sanm_check(m_pending < 0);
         rt::dzero(m_out.ptr(), m_out.size() * sizeof(double));
     } else {
-        sanm_check(m_pending == kb - 1 || m_pending < 0);
-        step(m_pending, kb, false);
+        sanm_check((m_pending == kb - 1 || m_pending < 0) && !m_pending_x);
+        step(m_pending, kb, false, nullptr);
         m_pending = -1;
     }
     m_out_is_bias = true;
 }
 
+void FusedProp::next_bias_to(int kb, double* b) {
+    sanm_check(m_io && kb >= 1 && kb <= m_K);
+    if (kb == 1) {
+        sanm_check(m_pending < 0);
+        rt::dzero(b, m_io->nout * sizeof(double));
+        return;
+    }
+    sanm_check(m_pending == kb - 1 && m_pending_x,
+               "fused I/O needs push_from before next_bias_to");
+    step(m_pending, kb, false, m_pending_x);
+    m_pending = -1;
+    m_pending_x = nullptr;
+    SANM_PROF("k_assemble_final");
+    m_io->finalize(b);
+}
+
 void FusedProp::jacobian(double* jac) {
     SANM_PROF("k_fused_jacobian");
-    KArgs a{m_arena.ptr(), m_aux.ptr(), m_ds.ptr(),  m_out.ptr(),
+    KArgs a{m_arena.ptr(), m_aux.ptr(),   m_ds.ptr(),  m_out.ptr(),
             m_dminv.ptr(), m_xbias.ptr(), m_err.ptr(), m_npad,
-            m_K + 1,       m_params};
+            m_n,           m_K + 1,       m_params};
     switch (m_mat) {
         case MAT_NHC:
             rt::for_each(m_n, JacKernel<NHC>{a, jac});

@@ -6,6 +6,7 @@
 #pragma once
 
 #include "fused_dev.h"
+#include "fused_io.h"
 #include "graph.h"
 
 namespace sanm_b200 {
@@ -44,6 +45,15 @@ public:
     void push(int k);
     //! bias of order kb = (last pushed order) + 1 into out_slot()
     void next_bias(int kb);
+    /* fused I/O (fused_io.h): the kernels gather from / assemble into nodal
+     * vectors themselves.  push_from(0, x0, fx) evaluates order 0 and
+     * assembles f(x0) into fx (may be null); push_from(k >= 1, xk) is deferred
+     * and next_bias_to(k + 1, b) runs coefficient phase k + bias phase k + 1 +
+     * assembly in one kernel (plus the small second-level reduction). */
+    void attach_io(std::shared_ptr<const FusedIO> io);
+    bool has_io() const { return (bool)m_io; }
+    void push_from(int k, const double* x, double* fx = nullptr);
+    void next_bias_to(int kb, double* b);
     //! d out / d in at the order-0 point, [N][9][9] row-major
     void jacobian(double* jac);
     int* err_flag() const { return m_err.ptr(); }
@@ -55,13 +65,15 @@ private:
     int64_t m_npad;
     int m_K, m_S;
     int m_pending = -1;  //!< order whose push has not been launched yet
+    const double* m_pending_x = nullptr;  //!< its nodal vector (fused I/O)
+    std::shared_ptr<const FusedIO> m_io;
     bool m_out_is_bias = false;
     rt::DBuf<double> m_arena, m_aux, m_ds, m_out, m_dminv, m_xbias;
     rt::DBuf<int> m_err;
 
     template <class M>
-    void launch_step(int k_push, int kb, bool want_out);
-    void step(int k_push, int kb, bool want_out);
+    void launch_step(int k_push, int kb, bool want_out, const double* x);
+    void step(int k_push, int kb, bool want_out, const double* x);
     void flush();
 };
 

@@ -34,6 +34,27 @@ public:
         const int K = m_order;
         TaylorProp& p = *m_prop;
         p.reset();
+        if (p.attach_io(*m_rin, *m_rout)) {
+            // gather and assembly inside the element kernels
+            {
+                SANM_PROF("push_xi");
+                p.push_xi_from(m_x.ptr(), m_b.ptr());
+            }
+            for (int k = 1; k <= K; ++k) {
+                {
+                    SANM_PROF("taylor_next_order");
+                    p.compute_next_order_bias_to(m_b.ptr() + (size_t)k * m_nout);
+                    // the reference computes the per-tet Jacobian inside its
+                    // first compute_next_order_bias (libsanm/symbolic.cpp:249-252)
+                    if (k == 1) p.ensure_jacobian();
+                }
+                if (k < K) {
+                    SANM_PROF("push_xi");
+                    p.push_xi_from(m_x.ptr() + (size_t)k * m_nin);
+                }
+            }
+            return;
+        }
         const VecLayout soa_in{p.in_elems(), p.npad()};
         const VecLayout soa_out{p.out_elems(), p.npad()};
         {

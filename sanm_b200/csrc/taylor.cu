@@ -2,6 +2,9 @@
  * (tetrahedron), walking the lowered operator list (taylor_dev.h). */
 #include "taylor.h"
 #include "prof.h"
+#include "remap.h"
+
+#include <cstdlib>
 
 namespace sanm_b200 {
 
@@ -325,6 +328,33 @@ void TaylorProp::compute_next_order_bias() {
     } else {
         launch(m_order, PH_BIAS, 0);
     }
+}
+
+bool TaylorProp::attach_io(const Remap& rin, const Remap& rout) {
+    if (!m_fused) return false;
+    if (m_fused->has_io()) return true;
+    const char* off = getenv("SANM_NO_FUSED_IO");
+    if (off && off[0] == '1') return false;
+    std::shared_ptr<const FusedIO> io = FusedIO::analyse(rin, rout, m_low.batch);
+    if (!io) return false;
+    m_fused->attach_io(std::move(io));
+    return true;
+}
+
+void TaylorProp::push_xi_from(const double* x, double* fx) {
+    sanm_check(m_prepared && m_fused && m_fused->has_io() && !m_xi_known);
+    if (m_order < 0) m_order = 0;
+    m_fused->push_from(m_order, x, fx);
+    m_xi_known = true;
+}
+
+void TaylorProp::compute_next_order_bias_to(double* b) {
+    sanm_check(m_prepared && m_fused && m_fused->has_io() && m_xi_known);
+    sanm_check(m_order + 1 <= m_max_order, "order %d exceeds max_order %d",
+               m_order + 1, m_max_order);
+    ++m_order;
+    m_xi_known = false;
+    m_fused->next_bias_to(m_order, b);
 }
 
 const double* TaylorProp::ensure_jacobian() {

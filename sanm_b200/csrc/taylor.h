@@ -47,6 +47,18 @@ public:
     //! increase the order and compute the bias of the output (phase A)
     void compute_next_order_bias();
 
+    /* fused I/O: when the graph runs on the fused element kernels and both
+     * remaps have the mesh structure of fused_io.h, the kernels gather from /
+     * assemble into nodal vectors themselves and the staging slots above are
+     * not used.  attach_io() returns false otherwise (callers keep the staged
+     * path: Remap::apply around push_xi_filled / compute_next_order_bias). */
+    bool attach_io(const class Remap& rin, const class Remap& rout);
+    //! push_xi(remap_in(x)); at order 0 also fx = remap_out(f(..)) if non-null.
+    //! x must stay valid until the next compute_next_order_bias_to()
+    void push_xi_from(const double* x, double* fx = nullptr);
+    //! b = remap_out(compute_next_order_bias())
+    void compute_next_order_bias_to(double* b);
+
     //! host-buffer conveniences (row-major [N, ...] as in the reference)
     void push_xi_host(const double* x, const Shape& shape);
     void output_to_host(int k, double* out) const;
