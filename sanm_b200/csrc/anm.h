@@ -48,8 +48,10 @@ public:
     const std::vector<uint32_t>& colidx() const { return m_colidx; }
     uint64_t nnz() const { return m_colidx.size(); }
     //! vals (device, nnz) and grad_t (device, n; may be null) from the
-    //! per-item Jacobian (device, [N][odim][idim] or [N][dim])
-    void assemble(double* vals, double* grad_t, const double* jac) const;
+    //! per-item Jacobian (device, [N][odim][idim] or [N][dim]; with
+    //! jac_pitch != 0 the FULL form is stored [odim*idim][jac_pitch])
+    void assemble(double* vals, double* grad_t, const double* jac,
+                  int64_t jac_pitch = 0) const;
 
 private:
     std::shared_ptr<const Remap> m_rin, m_rout;
@@ -125,6 +127,9 @@ private:
     size_t m_iter = 0;
     double m_t_max = 0, m_t_max_a = 0;
     std::unique_ptr<PadeApproximation> m_pade;
+    bool m_fx_check_failed = false;
+    double m_a_bound_taylor = 0;
+    size_t m_nr_pade_rejected = 0;
     bool m_converged = false;
     double m_residual_rms = 0;
     Stats m_stats;

@@ -142,12 +142,7 @@ int sanm_prop_get_jacobian(sanm_prop_t* p, int* type, uint64_t* batch,
         *batch = p->p->batch();
         *odim = p->p->out_elems();
         *idim = p->p->in_elems();
-        if (out) {
-            const double* j = p->p->ensure_jacobian();
-            size_t n = *batch * *odim *
-                       (*type == TaylorProp::JAC_FULL ? *idim : 1);
-            rt::d2h(out, j, n * sizeof(double));
-        }
+        if (out) p->p->jacobian_to_host(out);
     });
 }
 int sanm_eval_unary_func(sanm_graph_t* g, int out_var, const double* x,

@@ -232,7 +232,8 @@ struct StepKernel {
     }
 };
 
-//! forward-mode Jacobian: nine unit tangents per tet, [N][9][9] row-major
+//! forward-mode Jacobian: nine unit tangents per tet, stored
+//! structure-of-arrays [81][npad] (entry o * 9 + j) so that stores coalesce
 template <class M>
 struct JacKernel {
     KArgs a;
@@ -243,7 +244,7 @@ struct JacKernel {
         ld_strided<S>(s0, slot_ptr<M>(a, t, 0));
         if (M::AUX) ld_strided<M::AUX>(aux, aux_ptr<M>(a, t));
         ld_soa<9>(dm, a.dminv, a.npad, t);
-        double* jt = jac + t * 81;
+        double* jt = jac + t;
         for (int j = 0; j < 9; ++j) {
             const int r0 = j / 3, m0 = j % 3;
             double ts[S], Pt[9];
@@ -253,7 +254,7 @@ struct JacKernel {
             for (int c = 0; c < 3; ++c) ts[r0 * 3 + c] = dm[m0 * 3 + c];
             M::tangent(ts, s0, aux, a.pr, ts, Pt);
 #pragma unroll
-            for (int o = 0; o < 9; ++o) jt[o * 9 + j] = Pt[o];
+            for (int o = 0; o < 9; ++o) jt[(int64_t)(o * 9 + j) * a.npad] = Pt[o];
         }
     }
 };

@@ -54,7 +54,7 @@ public:
     bool has_io() const { return (bool)m_io; }
     void push_from(int k, const double* x, double* fx = nullptr);
     void next_bias_to(int kb, double* b);
-    //! d out / d in at the order-0 point, [N][9][9] row-major
+    //! d out / d in at the order-0 point, [81][npad] (entry o * 9 + i)
     void jacobian(double* jac);
     int* err_flag() const { return m_err.ptr(); }
 

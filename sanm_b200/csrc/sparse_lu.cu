@@ -1,6 +1,8 @@
 /* sanm_b200/csrc/sparse_lu.cu -- numeric multifrontal factorisation and solves
  * (see sparse_lu.h for the algorithm). */
 #include "sparse_lu.h"
+
+#include <cstdlib>
 #include "sparse_symbolic.h"
 
 #include <algorithm>
@@ -13,7 +15,6 @@ namespace {
 constexpr int NB = 32;          //!< pivot block of the large-front path
 constexpr uint32_t SMALL_NR = 104;  //!< fronts up to this size live in smem
 constexpr int ASM_TILE = 4096;  //!< entries per assembly task
-constexpr int ROW_CHUNK = 256;  //!< rows per solve task
 
 struct FrontD {
     double* F;        //!< nr x nr, column-major
@@ -340,32 +341,48 @@ struct BigColPanelKernel {
 
 /* ---- solves */
 
-struct PermuteIn {
-    double* dst;
-    const double* src;
-    const uint32_t* perm;
-    SANM_D void operator()(size_t i) const { dst[i] = src[perm[i]]; }
-};
-struct PermuteOut {
-    double* dst;
-    const double* src;
-    const uint32_t* perm;
-    SANM_D void operator()(size_t i) const { dst[perm[i]] = src[i]; }
-};
+/* Solve kernels.  A task is one chunk of SOLVE_ROWS rows of one front; a
+ * block of SOLVE_THREADS threads = SOLVE_WARPS groups of 32 lanes.  Lane l owns
+ * row l of the chunk (column-major fronts: the 32 lanes read 32 consecutive
+ * doubles), group g accumulates columns g, g + SOLVE_WARPS, ... with four
+ * independent accumulators, and the groups' partial sums are added in fixed
+ * order through shared memory, so results are bitwise reproducible and a
+ * dense front of any size spreads over nr/32 blocks x 8 warps. */
+constexpr int SOLVE_ROWS = 32;
+constexpr int SOLVE_WARPS = 8;
+constexpr int SOLVE_THREADS = SOLVE_ROWS * SOLVE_WARPS;
 
-//! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates
+//! partial dot products of rows [r0, r0+32) of a column-major block with v
+SANM_HD inline double solve_partial(const double* col0, uint64_t ld,
+                                    uint32_t ncol, const double* v, int g) {
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    uint32_t j = g;
+    for (; j + 3 * SOLVE_WARPS < ncol; j += 4 * SOLVE_WARPS) {
+        a0 += col0[(uint64_t)j * ld] * v[j];
+        a1 += col0[(uint64_t)(j + SOLVE_WARPS) * ld] * v[j + SOLVE_WARPS];
+        a2 += col0[(uint64_t)(j + 2 * SOLVE_WARPS) * ld] * v[j + 2 * SOLVE_WARPS];
+        a3 += col0[(uint64_t)(j + 3 * SOLVE_WARPS) * ld] * v[j + 3 * SOLVE_WARPS];
+    }
+    for (; j < ncol; j += SOLVE_WARPS) a0 += col0[(uint64_t)j * ld] * v[j];
+    return (a0 + a1) + (a2 + a3);
+}
+
+//! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates;
+//! b is read through the fill-reducing permutation
 struct ForwardKernel {
     const FrontD* fronts;
     const uint32_t* child_list;
     const Task* tasks;
-    const double* bp;  // permuted right-hand side
+    const double* b;       // right-hand side, original numbering
+    const uint32_t* perm;  // new index -> original index
     SANM_D void operator()(const rt::BlockCtx& c) const {
         const Task tk = tasks[c.bid];
         const FrontD f = fronts[tk.front];
         double* w1 = reinterpret_cast<double*>(c.smem);
         double* w1p = w1 + f.nc;
+        double* part = w1p + f.nc;
         for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
-            double v = bp[f.c0 + i];
+            double v = b[perm[f.c0 + i]];
             for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
                 const FrontD ch = fronts[child_list[q]];
                 const int32_t ii = ch.inv[i];
@@ -380,47 +397,59 @@ struct ForwardKernel {
         }
         c.sync();
         const uint32_t nu = f.nr - f.nc;
-        const uint32_t r0 = tk.chunk * ROW_CHUNK;
-        const uint32_t r1 = r0 + ROW_CHUNK < nu ? r0 + ROW_CHUNK : nu;
-        for (uint32_t i = r0 + c.tid; i < r1; i += c.nthr) {
+        const uint32_t r0 = tk.chunk * SOLVE_ROWS;
+        for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
+            const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
+            const uint32_t r = r0 + lane;
+            part[th] = r < nu ? solve_partial(f.F + f.nc + r, f.nr, f.nc, w1p, g)
+                              : 0.0;
+        }
+        c.sync();
+        for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
+            const uint32_t r = r0 + lane;
+            if (r >= nu) continue;
             double acc = 0;
             for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
                 const FrontD ch = fronts[child_list[q]];
-                const int32_t ii = ch.inv[f.nc + i];
+                const int32_t ii = ch.inv[f.nc + r];
                 if (ii >= 0) acc += ch.vec[ch.nc + ii];
             }
-            const double* row = f.F + f.nc + i;
-            for (uint32_t j = 0; j < f.nc; ++j) {
-                acc += row[(uint64_t)j * f.nr] * w1p[j];
-            }
-            f.vec[f.nc + i] = acc;
+            for (int g = 0; g < SOLVE_WARPS; ++g) acc += part[g * SOLVE_ROWS + lane];
+            f.vec[f.nc + r] = acc;
         }
     }
 };
 
-//! backward: x1 = G w1' - F12' x2
+//! backward: x1 = G w1' - F12' x2, written to the permuted work vector (read
+//! by descendants) and to the caller's vector in original numbering
 struct BackwardKernel {
     const FrontD* fronts;
     const Task* tasks;
     double* xp;  // permuted solution
+    double* x;   // solution, original numbering
+    const uint32_t* perm;
     SANM_D void operator()(const rt::BlockCtx& c) const {
         const Task tk = tasks[c.bid];
         const FrontD f = fronts[tk.front];
-        double* w1p = reinterpret_cast<double*>(c.smem);
-        double* x2 = w1p + f.nc;
-        const uint32_t nu = f.nr - f.nc;
-        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) w1p[i] = f.vec[i];
-        for (uint32_t i = c.tid; i < nu; i += c.nthr) x2[i] = xp[f.st[f.nc + i]];
+        double* v = reinterpret_cast<double*>(c.smem);  // [w1' ; -x2]
+        double* part = v + f.nr;
+        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) v[i] = f.vec[i];
+        for (uint32_t i = f.nc + c.tid; i < f.nr; i += c.nthr) v[i] = -xp[f.st[i]];
         c.sync();
-        const uint32_t r0 = tk.chunk * ROW_CHUNK;
-        const uint32_t r1 = r0 + ROW_CHUNK < f.nc ? r0 + ROW_CHUNK : f.nc;
-        for (uint32_t i = r0 + c.tid; i < r1; i += c.nthr) {
-            const double* row = f.F + i;
+        const uint32_t r0 = tk.chunk * SOLVE_ROWS;
+        for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
+            const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
+            const uint32_t r = r0 + lane;
+            part[th] = r < f.nc ? solve_partial(f.F + r, f.nr, f.nr, v, g) : 0.0;
+        }
+        c.sync();
+        for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
+            const uint32_t r = r0 + lane;
+            if (r >= f.nc) continue;
             double acc = 0;
-            for (uint32_t j = 0; j < f.nc; ++j) acc += row[(uint64_t)j * f.nr] * w1p[j];
-            const double* row2 = row + (uint64_t)f.nc * f.nr;
-            for (uint32_t j = 0; j < nu; ++j) acc -= row2[(uint64_t)j * f.nr] * x2[j];
-            xp[f.c0 + i] = acc;
+            for (int g = 0; g < SOLVE_WARPS; ++g) acc += part[g * SOLVE_ROWS + lane];
+            xp[f.c0 + r] = acc;
+            x[perm[f.c0 + r]] = acc;
         }
     }
 };
@@ -549,9 +578,9 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                 L.big_max_nc = std::max(L.big_max_nc, nc);
                 L.big_max_nr = std::max(L.big_max_nr, nr);
             }
-            uint32_t nf = std::max<uint32_t>(1, (nu + ROW_CHUNK - 1) / ROW_CHUNK);
+            uint32_t nf = std::max<uint32_t>(1, (nu + SOLVE_ROWS - 1) / SOLVE_ROWS);
             for (uint32_t t = 0; t < nf; ++t) fwd_t.push_back({s, t});
-            uint32_t nbk = (nc + ROW_CHUNK - 1) / ROW_CHUNK;
+            uint32_t nbk = (nc + SOLVE_ROWS - 1) / SOLVE_ROWS;
             for (uint32_t t = 0; t < nbk; ++t) bwd_t.push_back({s, t});
             L.max_nc = std::max(L.max_nc, nc);
             L.max_nr = std::max(L.max_nr, nr);
@@ -568,6 +597,27 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.small_list.upload(small_l);
     I.big_list.upload(big_l);
 
+    if (getenv("SANM_LU_DEBUG")) {
+        printf("[lu] n=%zu nnz=%zu nsn=%u levels=%u factor_entries=%zu "
+               "front_total=%zu flops=%.3g max_front=%u\n",
+               (size_t)n, (size_t)m_nnz, S.nsn, nlev, (size_t)S.factor_entries,
+               (size_t)S.front_total, S.flops, max_front);
+        for (uint32_t l = 0; l < nlev; ++l) {
+            uint32_t cnt = S.level_ptr[l + 1] - S.level_ptr[l], mnc = 0, mnr = 0;
+            uint64_t ent = 0;
+            for (uint32_t q = S.level_ptr[l]; q < S.level_ptr[l + 1]; ++q) {
+                uint32_t s = S.level_list[q];
+                mnc = std::max(mnc, S.sn_nc[s]);
+                mnr = std::max(mnr, S.sn_nr[s]);
+                ent += (uint64_t)S.sn_nc[s] * (2 * S.sn_nr[s] - S.sn_nc[s]);
+            }
+            printf("[lu]  level %2u: fronts=%5u max_nc=%4u max_nr=%4u "
+                   "entries=%9zu fwd_tasks=%u bwd_tasks=%u\n",
+                   l, cnt, mnc, mnr, (size_t)ent, I.levels[l].fwd_n,
+                   I.levels[l].bwd_n);
+        }
+        fflush(stdout);
+    }
     m_stats = {};
     m_stats.n = n;
     m_stats.nnz_a = m_nnz;
@@ -633,21 +683,24 @@ void SparseLU::factor(const double* vals_dev) {
 void SparseLU::solve(double* x_dev, const double* b_dev) {
     Impl& I = *m_impl;
     sanm_check(I.factored, "solve() before factor()");
-    rt::for_each(m_n, PermuteIn{I.bp.ptr(), b_dev, I.perm.ptr()});
+    // b may alias x: the forward sweep has consumed b before the backward
+    // sweep writes x
     for (auto& L : I.levels) {
-        rt::for_each_block(L.fwd_n, 128, 2 * (size_t)L.max_nc * sizeof(double),
-                           ForwardKernel{I.fd.ptr(), I.child_list.ptr(),
-                                         I.fwd_tasks.ptr() + L.fwd_off,
-                                         I.bp.ptr()});
+        rt::for_each_block(
+                L.fwd_n, SOLVE_THREADS,
+                (2 * (size_t)L.max_nc + SOLVE_THREADS) * sizeof(double),
+                ForwardKernel{I.fd.ptr(), I.child_list.ptr(),
+                              I.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                              I.perm.ptr()});
     }
     for (size_t l = I.levels.size(); l-- > 0;) {
         auto& L = I.levels[l];
-        rt::for_each_block(L.bwd_n, 128, (size_t)L.max_nr * sizeof(double),
-                           BackwardKernel{I.fd.ptr(),
-                                          I.bwd_tasks.ptr() + L.bwd_off,
-                                          I.xp.ptr()});
+        rt::for_each_block(
+                L.bwd_n, SOLVE_THREADS,
+                ((size_t)L.max_nr + SOLVE_THREADS) * sizeof(double),
+                BackwardKernel{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
+                               I.xp.ptr(), x_dev, I.perm.ptr()});
     }
-    rt::for_each(m_n, PermuteOut{x_dev, I.xp.ptr(), I.perm.ptr()});
 }
 
 void SparseLU::apply(double* y_dev, const double* x_dev) const {

@@ -361,7 +361,7 @@ const double* TaylorProp::ensure_jacobian() {
     if (m_jac_done) return m_jac.ptr();
     if (m_fused) {
         sanm_check(m_order >= 0, "Jacobian needs the order-0 point");
-        m_jac.ensure(m_low.batch * 81);
+        m_jac.ensure((size_t)81 * m_npad);
         m_fused->jacobian(m_jac.ptr());
         m_jac_done = true;
         return m_jac.ptr();
@@ -390,6 +390,20 @@ const double* TaylorProp::ensure_jacobian() {
     m_in_jacobian = false;
     m_jac_done = true;
     return m_jac.ptr();
+}
+
+void TaylorProp::jacobian_to_host(double* out) {
+    const double* j = ensure_jacobian();
+    const uint64_t n = m_low.batch;
+    const size_t per = jacobian_type() == JAC_FULL
+                               ? (size_t)out_elems() * in_elems()
+                               : (size_t)out_elems();
+    if (jacobian_pitch()) {
+        m_stage.ensure(n * per);
+        soa_to_aos(m_stage.ptr(), j, n, (int)per, jacobian_pitch());
+        j = m_stage.ptr();
+    }
+    rt::d2h(out, j, n * per * sizeof(double));
 }
 
 void TaylorProp::push_xi_host(const double* x, const Shape& shape) {

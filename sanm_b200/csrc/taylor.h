@@ -76,6 +76,11 @@ public:
         return m_low.elemwise ? JAC_ELEMWISE : JAC_FULL;
     }
     const double* ensure_jacobian();
+    //! 0: the FULL Jacobian is [N][odim][idim]; otherwise it is stored
+    //! structure-of-arrays [odim*idim][pitch] (fused element kernels)
+    int64_t jacobian_pitch() const { return m_fused ? m_npad : 0; }
+    //! copy the Jacobian to a host buffer in the reference's layout
+    void jacobian_to_host(double* out);
 
     //! throw SANM_ERR_NUMERICAL if a kernel flagged 0^p with non-integer p;
     //! synchronises the stream

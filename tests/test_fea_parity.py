@@ -43,7 +43,7 @@ def cuboid_body(binding, dims, energy, delta=False, partial_fix=False):
         body.coord_fixed_mask[vx >= 0.025 * (nx - 1.5)] = True
         vtx_delta = np.zeros_like(mesh.vertices)
         far = vx >= 0.025 * (nx - 1.5)
-        vtx_delta[far] = np.array([0.01, 0.02, -0.015])
+        vtx_delta[far] = np.array([0.01, 0.02, -0.015]) * float(delta)
     model = body.make_forward(energy, None, vtx_delta)
     return mesh, body, model
 
@@ -172,3 +172,31 @@ def test_implicit_solve_cuboid(impl, ref, path, monkeypatch):
     # (fea/main.cpp:551-574); the 1e-7 bar applies after that refinement
     assert abs(t - 1) < 1e-5 and abs(rt - 1) < 1e-5
     assert np.abs(x - rx).max() <= 1e-5 * np.abs(rx).max()
+
+
+def test_pade_rejection_recovery(impl, monkeypatch, capfd):
+    """When the consistency check of an expansion fails after a Pade jump the
+    reference aborts (libsanm/anm.cpp:509-518); this library steps back to the
+    range of the plain series and continues.  The recovery path is forced once
+    through SANM_INJECT_PADE_REJECT and must still reach t = 1 at the same
+    point as an undisturbed run."""
+    def run():
+        # a displacement large enough to need several continuation steps
+        _, _, model = cuboid_body(impl, (7, 3, 3), mat.NEOHOOKEAN_C, delta=6.0)
+        hyper = Hyper(order=10, use_pade=1, solution_check_tol=1.0)
+        s = ANMImplicitSolver(model.y, model.lt_inp.desc, model.lt_out,
+                              model.lt_inp.x0, 0.0, hyper)
+        it = 0
+        while s.get_t_upper() < 1 and it < 30:
+            s.update_approx()
+            it += 1
+        x, t = s.eval(s.solve_a(1.0))
+        return it, x, t
+
+    it0, x0, t0 = run()
+    monkeypatch.setenv("SANM_INJECT_PADE_REJECT", "1")
+    it1, x1, t1 = run()
+    assert "rejected" in capfd.readouterr().err
+    assert it0 >= 1 and it1 >= it0
+    assert abs(t1 - 1) < 1e-5
+    assert np.abs(x1 - x0).max() <= 1e-5 * np.abs(x0).max()

@@ -1,0 +1,35 @@
+#!/usr/bin/env python
+"""Per-tag device/host time of one fea config on the GPU path:
+    python tools/solve_profile.py bob.json [override.json ...]
+(config names are resolved in oracle/_ref/config)."""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import sanm_b200  # noqa: E402
+from sanm_b200 import fea  # noqa: E402
+
+CONFIG_DIR = os.path.join(ROOT, "oracle", "_ref", "config")
+
+
+def main():
+    b = sanm_b200.load()
+    task = os.path.join(CONFIG_DIR, sys.argv[1])
+    ovs = [os.path.join(CONFIG_DIR, o) for o in sys.argv[2:]]
+    for rep in range(2):  # second run: warm allocator / module load
+        b.prof_reset()
+        t0 = time.perf_counter()
+        res = fea.run_task(b, task, ovs, save=False,
+                           log=fea.RunLog(verbose=False))
+        wall = time.perf_counter() - t0
+    st = res[1]
+    print("wall_s", wall)
+    print("stats", st if not isinstance(st, list) else
+          [{k: s[k] for k in ("iter_tot", "time")} for s in st])
+    print(b.prof_dump())
+
+
+if __name__ == "__main__":
+    main()
