@@ -83,10 +83,13 @@ def make_series(x0: np.ndarray, order: int, seed: int = 92702102):
     return x
 
 
-def cuboid_model(binding, nx, ny, nz, energy, spacing=0.025):
-    """the cuboid-twist body of fea/main.cpp:665-690 (both end faces fixed)"""
+def cuboid_model(binding, nx, ny, nz, energy, spacing=0.025,
+                 cube_x_range=None):
+    """the cuboid-twist body of fea/main.cpp:665-690 (both end faces fixed);
+    cube_x_range: this rank's slab of hexahedra (all vertices are kept)"""
     from sanm_b200 import fea, material as mat
-    mesh = fea.TetrahedralMesh.make_cuboid(nx, ny, nz, spacing)
+    mesh = fea.TetrahedralMesh.make_cuboid(nx, ny, nz, spacing,
+                                           cube_x_range=cube_x_range)
     body = fea.DeformableBody(
         binding, mat.MaterialProperty.from_young_poisson(1e7, 0.45), mesh)
     vx = mesh.vertices[:, 0]
@@ -225,12 +228,17 @@ def run_reference_arm(args):
     os._exit(0)  # skip the reference's exit-time profiler report on stdout
 
 
-def workload_config(args, tets_per_gpu):
+def workload_config(args, tets_per_gpu, world=1):
     return {"workload": ("synthetic scaled tet cuboid (cuboid_twist family), "
                          "element phase of one order-%d series expansion: "
-                         "gather + Taylor bias/coeff + assembly" % ORDER),
+                         "gather + Taylor bias/coeff + Jacobian + assembly; "
+                         "N GPUs: one cuboid %dx longer, tets sharded by "
+                         "x-slab, nodal right-hand sides summed by NCCL "
+                         "all-reduce every order" % (ORDER, world)),
             "energy_model": args.energy, "order": ORDER,
             "cuboid_vertices_per_gpu": [args.nx, args.ny, args.nz],
+            "cuboid_vertices_global": [(args.nx - 1) * world + 1, args.ny,
+                                       args.nz],
             "tets_per_gpu": int(tets_per_gpu),
             "l2": "Taylor stacks per GPU exceed the 126 MB L2 (no flush needed)"}
 
@@ -315,13 +323,22 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- workload: every rank owns one cuboid shard of identical size (weak)
-    mesh, model = cuboid_model(b, args.nx, args.ny, args.nz, args.energy)
+    # ---- workload (weak scaling): ONE cuboid, `world` times longer in x; each
+    # rank owns the tets of one x-slab (a contiguous range of the element
+    # list), all ranks hold the full nodal vectors and the assembled
+    # right-hand side of every order is summed over the ranks (csrc/comm.h)
+    if world > 1:
+        from sanm_b200 import dist as sdist
+        sdist.init_comm(b)
+    nxg = (args.nx - 1) * world + 1
+    mesh, model = cuboid_model(
+        b, nxg, args.ny, args.nz, args.energy,
+        cube_x_range=(rank * (args.nx - 1), (rank + 1) * (args.nx - 1)))
     n_tets = mesh.nr_tet
     n = model.lt_inp.nr_unknown_vtx
     sweep = ElementSweep(model.y, model.lt_inp.desc, model.lt_out, ORDER)
     x_t, x_host = pinned_empty((ORDER + 1, n))
-    x_host[:] = make_series(model.lt_inp.x0, ORDER, seed=92702102 + rank)
+    x_host[:] = make_series(model.lt_inp.x0, ORDER, seed=92702102)
     b_t, b_host = pinned_empty((ORDER + 1, n))
     sweep.set_x(x_host)
     st = sweep.stats()
@@ -346,7 +363,8 @@ def run_ours(args):
     prof = {t: b.prof_get(t) for t in
             ("taylor_next_order", "push_xi", "remap_out", "k_order_bias",
              "k_order_coef", "k_order_eval", "k_jacobian", "k_fused_eval",
-             "k_fused_step", "k_fused_jacobian")}
+             "k_fused_step", "k_fused_jacobian", "k_assemble_final",
+             "comm_allreduce")}
     clocks = sampler.stop()
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region
@@ -394,10 +412,10 @@ def run_ours(args):
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, n_tets),
+        "config": workload_config(args, n_tets, world),
         "e2e": {"value": e2e, "unit": "tet*order/s",
-                "h2d_bytes_per_step": int(x_host.nbytes),
-                "d2h_bytes_per_step": int(b_host.nbytes)},
+                "h2d_bytes_per_step": int(x_host.nbytes) * world,
+                "d2h_bytes_per_step": int(b_host.nbytes) * world},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {

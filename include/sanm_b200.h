@@ -62,6 +62,25 @@ int sanm_prof_reset(void);
 /* accumulated milliseconds and call count of one tag; 0/0 if never seen */
 int sanm_prof_get(const char* tag, double* ms, uint64_t* calls);
 
+/* ---- multi-GPU: one process per GPU, tets sharded over the ranks ----------
+ * Replaces the worker threads of ParallelTaylorCoeffProp
+ * (libsanm/symbolic.cpp:306-556: contiguous batch ranges, gather by memcpy).
+ * After sanm_comm_init_*() every solver / sweep created by this process
+ * propagates only its shard of the tets and sums the assembled nodal vectors
+ * (and the CSR values of K) over the ranks; see csrc/comm.h.
+ *   - NCCL: rank 0 calls sanm_comm_unique_id(), the 128 bytes are broadcast by
+ *     the caller (e.g. torch.distributed), every rank calls
+ *     sanm_comm_init_nccl();
+ *   - callback: the caller supplies the in-place sum over ranks of a host
+ *     vector (used by the CPU-only tests over gloo). */
+typedef void (*sanm_allreduce_fn)(double* buf, uint64_t n);
+int sanm_comm_unique_id(char* out128);
+int sanm_comm_init_nccl(const char* id128, int rank, int world);
+int sanm_comm_init_callback(sanm_allreduce_fn fn, int rank, int world);
+int sanm_comm_finalize(void);
+int sanm_comm_rank(int* rank, int* world);
+int sanm_comm_allreduce_host(double* buf, uint64_t n);
+
 /* ---- symbolic graph: libsanm/symbolic.h:283-293, libsanm/oprs.h:14-105 ---- */
 /* variables are small integers local to their graph (a VarNode* identity) */
 int sanm_graph_create(sanm_graph_t** out);

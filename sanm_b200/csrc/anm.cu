@@ -1,5 +1,7 @@
 /* sanm_b200/csrc/anm.cu -- see anm.h. */
 #include "anm.h"
+#include "comm.h"
+#include "shard.h"
 #include "poly.h"
 #include "prof.h"
 
@@ -242,9 +244,13 @@ struct AssembleK {
 
 KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
                        std::shared_ptr<const Remap> rout, uint64_t n,
-                       uint64_t batch, int odim, int idim, bool elemwise)
+                       uint64_t batch, int odim, int idim, bool elemwise,
+                       std::shared_ptr<const Remap> asm_rin,
+                       std::shared_ptr<const Remap> asm_rout)
         : m_rin{std::move(rin)},
           m_rout{std::move(rout)},
+          m_asm_rin{asm_rin ? std::move(asm_rin) : m_rin},
+          m_asm_rout{asm_rout ? std::move(asm_rout) : m_rout},
           m_n{n},
           m_batch{batch},
           m_odim{odim},
@@ -312,9 +318,9 @@ void KAssembler::assemble(double* vals, double* grad_t, const double* jac,
                           int64_t jac_pitch) const {
     sanm_check(!jac_pitch || !m_elemwise);
     rt::for_each(m_n, AssembleK{m_d_rowptr.ptr(), m_d_colidx.ptr(),
-                                m_rout->d_rowptr(), m_rout->d_idx(),
-                                m_rout->d_coeff(), m_rin->d_rowptr(),
-                                m_rin->d_idx(), m_rin->d_coeff(), jac,
+                                m_asm_rout->d_rowptr(), m_asm_rout->d_idx(),
+                                m_asm_rout->d_coeff(), m_asm_rin->d_rowptr(),
+                                m_asm_rin->d_idx(), m_asm_rin->d_coeff(), jac,
                                 jac_pitch, vals,
                                 grad_t, (uint32_t)m_n, m_odim, m_idim,
                                 (int)m_elemwise});
@@ -359,7 +365,24 @@ AnmSolver::AnmSolver(Kind kind, std::shared_ptr<const Graph> graph, int f,
                    m_rout->out_shape().str().c_str(), v_shape.str().c_str());
         m_v_host.assign(v, v + m_n);
     }
-    m_prop.reset(new TaylorProp{m_graph, f, hyper.order});
+    // multi-GPU: this rank propagates a contiguous range of the batch
+    // (libsanm/symbolic.cpp:525-529); nodal vectors stay global
+    m_graph_e = m_graph;
+    m_rin_e = m_rin;
+    m_rout_e = m_rout;
+    {
+        const uint64_t N = m_rin->out_shape().dim[0];
+        if (comm::world() > 1 && N >= (uint64_t)comm::world() &&
+            m_rout->in_shape().dim[0] == N) {
+            uint64_t lo, hi;
+            comm::shard_range(N, comm::rank(), comm::world(), &lo, &hi);
+            m_graph_e = shard_graph(*m_graph, N, lo, hi);
+            m_rin_e = shard_remap_rows(*m_rin, N, lo, hi);
+            m_rout_e = shard_remap_cols(*m_rout, N, lo, hi);
+            m_sharded = true;
+        }
+    }
+    m_prop.reset(new TaylorProp{m_graph_e, f, hyper.order});
 
     m_xt0.assign(x0, x0 + m_n);
     m_xt0.push_back(kind == EQN ? 0.0 : t0);
@@ -466,12 +489,16 @@ void AnmSolver::solve_expansion_coeffs() {
     rt::h2d(m_d_xt.ptr(), m_xt0.data(), (n + 1) * sizeof(double));
     m_nr_coeffs = 1;
 
-    const Shape elem_shape = m_rin->out_shape();
+    const Shape elem_shape = m_rin_e->out_shape();
     m_prop->prepare(elem_shape);
-    sanm_check(m_rout->nr_in() == m_prop->batch() * m_prop->out_elems(),
+    sanm_check(m_rout_e->nr_in() == m_prop->batch() * m_prop->out_elems(),
                "remap_out input size does not match the function output");
     // fused I/O: gather and assembly happen inside the element kernels
-    const bool fio = m_prop->attach_io(*m_rin, *m_rout);
+    const bool fio = m_prop->attach_io(*m_rin_e, *m_rout_e);
+    // sum over the ranks of a nodal vector assembled from the local tets
+    auto reduce = [&](double* v, size_t len) {
+        if (m_sharded) comm::allreduce_sum(v, len);
+    };
     const VecLayout soa_in{m_prop->in_elems(), m_prop->npad()};
     const VecLayout soa_out{m_prop->out_elems(), m_prop->npad()};
     if (fio) {
@@ -480,13 +507,15 @@ void AnmSolver::solve_expansion_coeffs() {
     } else {
         {
             SANM_PROF("push_xi");
-            m_rin->apply(m_prop->input_slot(0), soa_in, m_d_xt.ptr(),
-                         VecLayout{});
+            m_rin_e->apply(m_prop->input_slot(0), soa_in, m_d_xt.ptr(),
+                           VecLayout{});
             m_prop->push_xi_filled();
         }
         SANM_PROF("remap_out");
-        m_rout->apply(m_d_fx.ptr(), VecLayout{}, m_prop->output_slot(0), soa_out);
+        m_rout_e->apply(m_d_fx.ptr(), VecLayout{}, m_prop->output_slot(0),
+                        soa_out);
     }
+    reduce(m_d_fx.ptr(), n);
     m_prop->check_device_error();
     if (!on_fx0_computed()) return;
 
@@ -513,21 +542,37 @@ void AnmSolver::solve_expansion_coeffs() {
                 if (!m_kasm) {
                     SANM_PROF("K_symbolic_host");
                     m_kasm.reset(new KAssembler{
-                            m_rin, m_rout, n, m_prop->batch(),
+                            m_rin, m_rout, n, m_rin->out_shape().dim[0],
                             m_prop->out_elems(), m_prop->in_elems(),
-                            m_prop->jacobian_type() == TaylorProp::JAC_ELEMWISE});
+                            m_prop->jacobian_type() == TaylorProp::JAC_ELEMWISE,
+                            m_rin_e, m_rout_e});
                     {
                         SANM_PROF("lu_analyze_host");
                         m_lu.analyze(n, m_kasm->rowptr().data(),
                                      m_kasm->colidx().data());
                     }
                     m_d_kvals.alloc(m_kasm->nnz());
+                    if (fio && m_prop->jacobian_pitch()) {
+                        SANM_PROF("K_elem_lists_host");
+                        m_kfused = FusedKAssembly::build(
+                                *m_prop->fused_io(), n, m_kasm->rowptr(),
+                                m_kasm->colidx());
+                    }
                 }
                 SANM_PROF("k_assemble_K");
-                m_kasm->assemble(m_d_kvals.ptr(),
-                                 m_kind == IMPLICIT ? m_d_grad_t.ptr() : nullptr,
-                                 m_prop->ensure_jacobian(),
-                                 m_prop->jacobian_pitch());
+                double* gt = m_kind == IMPLICIT ? m_d_grad_t.ptr() : nullptr;
+                if (m_kfused) {
+                    m_kfused->assemble(m_d_kvals.ptr(), gt,
+                                       m_prop->ensure_jacobian(),
+                                       m_prop->jacobian_pitch(),
+                                       *m_prop->fused_io());
+                } else {
+                    m_kasm->assemble(m_d_kvals.ptr(), gt,
+                                     m_prop->ensure_jacobian(),
+                                     m_prop->jacobian_pitch());
+                }
+                reduce(m_d_kvals.ptr(), m_kasm->nnz());
+                if (gt) reduce(gt, n);
             }
             {
                 SANM_PROF("sparse_prep");
@@ -544,9 +589,10 @@ void AnmSolver::solve_expansion_coeffs() {
         } else {
             if (!fio) {
                 SANM_PROF("remap_out");
-                m_rout->apply(m_d_bi.ptr(), VecLayout{}, m_prop->output_slot(i),
-                              soa_out);
+                m_rout_e->apply(m_d_bi.ptr(), VecLayout{},
+                                m_prop->output_slot(i), soa_out);
             }
+            reduce(m_d_bi.ptr(), n);
             {
                 SANM_PROF("sparse_solve");
                 m_lu.solve(m_d_xbi.ptr(), m_d_bi.ptr());
@@ -575,7 +621,7 @@ void AnmSolver::solve_expansion_coeffs() {
             if (fio) {
                 m_prop->push_xi_from(xti);
             } else {
-                m_rin->apply(m_prop->input_slot(i), soa_in, xti, VecLayout{});
+                m_rin_e->apply(m_prop->input_slot(i), soa_in, xti, VecLayout{});
                 m_prop->push_xi_filled();
             }
         }

@@ -43,7 +43,9 @@ public:
      */
     KAssembler(std::shared_ptr<const Remap> rin,
                std::shared_ptr<const Remap> rout, uint64_t n, uint64_t batch,
-               int odim, int idim, bool elemwise);
+               int odim, int idim, bool elemwise,
+               std::shared_ptr<const Remap> asm_rin = nullptr,
+               std::shared_ptr<const Remap> asm_rout = nullptr);
     const std::vector<uint32_t>& rowptr() const { return m_rowptr; }
     const std::vector<uint32_t>& colidx() const { return m_colidx; }
     uint64_t nnz() const { return m_colidx.size(); }
@@ -54,12 +56,36 @@ public:
                   int64_t jac_pitch = 0) const;
 
 private:
-    std::shared_ptr<const Remap> m_rin, m_rout;
+    std::shared_ptr<const Remap> m_rin, m_rout;  //!< define the pattern
+    //! the maps the numeric assembly runs over (a rank's shard of the items,
+    //! local item numbering; default: the same maps)
+    std::shared_ptr<const Remap> m_asm_rin, m_asm_rout;
     uint64_t m_n, m_batch;
     int m_odim, m_idim;
     bool m_elemwise;
     std::vector<uint32_t> m_rowptr, m_colidx;
     rt::DBuf<uint32_t> m_d_rowptr, m_d_colidx;
+};
+
+//! element-wise K assembly for the mesh remaps of fea (k_assemble.cu)
+class FusedKAssembly {
+public:
+    //! nullptr when the structure does not fit (a tet reading more than 13
+    //! distinct unknowns, 32-bit index overflow)
+    static std::unique_ptr<FusedKAssembly> build(
+            const FusedIO& io, uint64_t n, const std::vector<uint32_t>& k_rowptr,
+            const std::vector<uint32_t>& k_colidx);
+    //! jac: [81][jac_pitch] (TaylorProp::ensure_jacobian of a fused graph)
+    void assemble(double* vals, double* grad_t, const double* jac,
+                  int64_t jac_pitch, const FusedIO& io) const;
+
+private:
+    FusedKAssembly() = default;
+    uint64_t m_n_tets = 0, m_nnz = 0, m_n = 0;
+    int64_t m_npad = 0;
+    rt::DBuf<uint8_t> m_tab;
+    rt::DBuf<uint32_t> m_kptr, m_ksrc;
+    rt::DBuf<double> m_cbuf;
 };
 
 class AnmSolver {
@@ -108,6 +134,10 @@ private:
     const AnmHyper m_hyper;
     std::shared_ptr<const Graph> m_graph;
     std::shared_ptr<const Remap> m_rin, m_rout;
+    //! element-phase view: this rank's shard when running on several GPUs
+    std::shared_ptr<const Graph> m_graph_e;
+    std::shared_ptr<const Remap> m_rin_e, m_rout_e;
+    bool m_sharded = false;
     const Shape m_x_shape;
     const uint64_t m_n;   //!< unknowns without t
     const uint64_t m_ld;  //!< pitch of one series vector (>= n + 1)
@@ -115,6 +145,7 @@ private:
 
     std::unique_ptr<TaylorProp> m_prop;
     std::unique_ptr<KAssembler> m_kasm;
+    std::unique_ptr<FusedKAssembly> m_kfused;
     SparseLU m_lu;
 
     // host state

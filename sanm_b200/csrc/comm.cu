@@ -1,0 +1,138 @@
+/* sanm_b200/csrc/comm.cu -- see comm.h. */
+#include "comm.h"
+#include "capi_util.h"
+#include "prof.h"
+
+#ifdef SANM_WITH_NCCL
+#include <nccl.h>
+#endif
+
+namespace sanm_b200 {
+namespace comm {
+
+namespace {
+int g_world = 1, g_rank = 0;
+sanm_allreduce_fn g_cb = nullptr;
+std::vector<double> g_stage;
+#ifdef SANM_WITH_NCCL
+ncclComm_t g_nccl = nullptr;
+#define SANM_NCCL_CHECK(x)                                                   \
+    do {                                                                     \
+        ncclResult_t r__ = (x);                                              \
+        if (r__ != ncclSuccess) {                                            \
+            sanm_throw(SANM_ERR_CUDA, "NCCL error at %s:%d: %s", __FILE__,   \
+                       __LINE__, ncclGetErrorString(r__));                   \
+        }                                                                    \
+    } while (0)
+#endif
+}  // namespace
+
+int world() { return g_world; }
+int rank() { return g_rank; }
+
+void allreduce_sum(double* dev, size_t n) {
+    if (g_world == 1 || !n) return;
+    SANM_PROF("comm_allreduce");
+#ifdef SANM_WITH_NCCL
+    if (g_nccl) {
+        rt::count_launch();
+        SANM_NCCL_CHECK(ncclAllReduce(dev, dev, n, ncclDouble, ncclSum, g_nccl,
+                                      rt::stream()));
+        return;
+    }
+#endif
+    sanm_check(g_cb, "multi-rank run without a communicator");
+#ifdef SANM_HOSTEMU
+    g_cb(dev, n);
+#else
+    g_stage.resize(n);
+    rt::d2h(g_stage.data(), dev, n * sizeof(double));
+    g_cb(g_stage.data(), n);
+    rt::h2d(dev, g_stage.data(), n * sizeof(double));
+#endif
+}
+
+}  // namespace comm
+}  // namespace sanm_b200
+
+using namespace sanm_b200;
+
+extern "C" {
+
+int sanm_comm_unique_id(char* out128) {
+    return capi::guard([&] {
+#ifdef SANM_WITH_NCCL
+        static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+        ncclUniqueId id;
+        SANM_NCCL_CHECK(ncclGetUniqueId(&id));
+        memcpy(out128, &id, 128);
+#else
+        (void)out128;
+        sanm_throw(SANM_ERR_GENERIC, "built without NCCL");
+#endif
+    });
+}
+
+int sanm_comm_init_nccl(const char* id128, int rank, int world) {
+    return capi::guard([&] {
+#ifdef SANM_WITH_NCCL
+        sanm_check(world >= 1 && rank >= 0 && rank < world);
+        rt::check_device();
+        if (comm::g_nccl) {
+            ncclCommDestroy(comm::g_nccl);
+            comm::g_nccl = nullptr;
+        }
+        ncclUniqueId id;
+        memcpy(&id, id128, 128);
+        SANM_NCCL_CHECK(ncclCommInitRank(&comm::g_nccl, world, id, rank));
+        comm::g_world = world;
+        comm::g_rank = rank;
+#else
+        (void)id128;
+        (void)rank;
+        (void)world;
+        sanm_throw(SANM_ERR_GENERIC, "built without NCCL");
+#endif
+    });
+}
+
+int sanm_comm_init_callback(sanm_allreduce_fn fn, int rank, int world) {
+    return capi::guard([&] {
+        sanm_check(fn && world >= 1 && rank >= 0 && rank < world);
+        comm::g_cb = fn;
+        comm::g_world = world;
+        comm::g_rank = rank;
+    });
+}
+
+int sanm_comm_finalize(void) {
+    return capi::guard([&] {
+#ifdef SANM_WITH_NCCL
+        if (comm::g_nccl) {
+            rt::sync();
+            ncclCommDestroy(comm::g_nccl);
+            comm::g_nccl = nullptr;
+        }
+#endif
+        comm::g_cb = nullptr;
+        comm::g_world = 1;
+        comm::g_rank = 0;
+    });
+}
+
+int sanm_comm_rank(int* rank, int* world) {
+    *rank = comm::g_rank;
+    *world = comm::g_world;
+    return 0;
+}
+
+/* test / diagnostics entry: in-place sum over ranks of a host vector */
+int sanm_comm_allreduce_host(double* buf, uint64_t n) {
+    return capi::guard([&] {
+        rt::DBuf<double> d;
+        d.upload(buf, n);
+        comm::allreduce_sum(d.ptr(), n);
+        d.download(buf, n);
+    });
+}
+}

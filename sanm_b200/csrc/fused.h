@@ -52,6 +52,7 @@ public:
      * assembly in one kernel (plus the small second-level reduction). */
     void attach_io(std::shared_ptr<const FusedIO> io);
     bool has_io() const { return (bool)m_io; }
+    const FusedIO* io() const { return m_io.get(); }
     void push_from(int k, const double* x, double* fx = nullptr);
     void next_bias_to(int kb, double* b);
     //! d out / d in at the order-0 point, [81][npad] (entry o * 9 + i)

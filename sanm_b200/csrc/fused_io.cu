@@ -113,6 +113,8 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
             io->gidx.upload(gidx);
             io->gcoef.upload(gcoef);
         }
+        io->h_uidx = std::move(uidx);
+        io->h_gidx = std::move(gidx);
     }
 
     /* ---------------- assembly */
@@ -274,6 +276,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
         std::vector<uint32_t> fill(fin_ptr.begin(), fin_ptr.end() - 1);
         for (uint64_t g = 0; g < R; ++g) fin_idx[fill[part_row[g]]++] = (uint32_t)g;
     }
+    io->h_grow = std::move(grow);
     io->nrm.upload(nrm);
     io->lrow.upload(lrow);
     io->blk_ptr.upload(blk_cnt);

@@ -48,6 +48,9 @@ struct FusedIO {
     rt::DBuf<uint32_t> fin_idx;  //!< partial ids of each output row
     rt::DBuf<double> partial;    //!< [nr_partial]
     uint64_t nr_partial = 0;
+    // ---- host copies for the element-wise K assembly (k_assemble.cu)
+    std::vector<uint32_t> h_uidx, h_gidx;  //!< as uidx / gidx above
+    std::vector<uint32_t> h_grow;          //!< [12][npad] global row of (d, c)
 
     //! nullptr when either map lacks the structure described above
     static std::unique_ptr<FusedIO> analyse(const Remap& rin, const Remap& rout,

@@ -4,6 +4,7 @@
  * ANMDriverHelper::solve_expansion_coeffs (libsanm/anm.cpp:205-290) with the
  * nodal series x_0..x_K supplied by the caller.  C ABI: sanm_sweep_*. */
 #include "capi_util.h"
+#include "comm.h"
 #include "prof.h"
 
 namespace sanm_b200 {
@@ -39,6 +40,7 @@ public:
             {
                 SANM_PROF("push_xi");
                 p.push_xi_from(m_x.ptr(), m_b.ptr());
+                comm::allreduce_sum(m_b.ptr(), m_nout);
             }
             for (int k = 1; k <= K; ++k) {
                 {
@@ -47,6 +49,7 @@ public:
                     // the reference computes the per-tet Jacobian inside its
                     // first compute_next_order_bias (libsanm/symbolic.cpp:249-252)
                     if (k == 1) p.ensure_jacobian();
+                    comm::allreduce_sum(m_b.ptr() + (size_t)k * m_nout, m_nout);
                 }
                 if (k < K) {
                     SANM_PROF("push_xi");
@@ -65,6 +68,7 @@ public:
         {
             SANM_PROF("remap_out");
             m_rout->apply(m_b.ptr(), VecLayout{}, p.output_slot(0), soa_out);
+            comm::allreduce_sum(m_b.ptr(), m_nout);
         }
         for (int k = 1; k <= K; ++k) {
             {
@@ -75,6 +79,7 @@ public:
                 SANM_PROF("remap_out");
                 m_rout->apply(m_b.ptr() + (size_t)k * m_nout, VecLayout{},
                               p.output_slot(k), soa_out);
+                comm::allreduce_sum(m_b.ptr() + (size_t)k * m_nout, m_nout);
             }
             if (k < K) {
                 SANM_PROF("push_xi");

@@ -53,6 +53,7 @@ public:
      * not used.  attach_io() returns false otherwise (callers keep the staged
      * path: Remap::apply around push_xi_filled / compute_next_order_bias). */
     bool attach_io(const class Remap& rin, const class Remap& rout);
+    const FusedIO* fused_io() const { return m_fused ? m_fused->io() : nullptr; }
     //! push_xi(remap_in(x)); at order 0 also fx = remap_out(f(..)) if non-null.
     //! x must stay valid until the next compute_next_order_bias_to()
     void push_xi_from(const double* x, double* fx = nullptr);

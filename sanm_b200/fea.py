@@ -25,7 +25,7 @@ import os
 import sys
 import time
 from dataclasses import dataclass, field
-from typing import Callable, Dict, List, Optional
+from typing import Callable, Dict, List, Optional, Tuple
 
 import numpy as np
 
@@ -128,10 +128,15 @@ class TetrahedralMesh:
 
     # ------------------------------------------------------------ builders
     @staticmethod
-    def make_cuboid(nx: int, ny: int, nz: int, size: float
+    def make_cuboid(nx: int, ny: int, nz: int, size: float,
+                    cube_x_range: Optional[Tuple[int, int]] = None
                     ) -> "TetrahedralMesh":
         """fea/tetrahedral_mesh.cpp:92-205 (5 tets per hexahedron), vectorised;
-        vertex and element numbering are the reference's"""
+        vertex and element numbering are the reference's.
+
+        ``cube_x_range=(c0, c1)`` keeps all vertices but only the tets of the
+        hexahedra with x index in [c0, c1): one rank's contiguous shard of the
+        element list in a multi-GPU run (tets are numbered x-major)."""
         assert nx >= 2 and ny >= 2 and nz >= 2 and size > 0
         ii, jj, kk = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz),
                                  indexing="ij")
@@ -142,7 +147,9 @@ class TetrahedralMesh:
         def vid(x, y, z):
             return (x * ny + y) * nz + z
 
-        ci, cj, ck = np.meshgrid(np.arange(nx - 1), np.arange(ny - 1),
+        cx0, cx1 = (0, nx - 1) if cube_x_range is None else cube_x_range
+        assert 0 <= cx0 < cx1 <= nx - 1
+        ci, cj, ck = np.meshgrid(np.arange(cx0, cx1), np.arange(ny - 1),
                                  np.arange(nz - 1), indexing="ij")
         ci, cj, ck = ci.reshape(-1), cj.reshape(-1), ck.reshape(-1)
         hexid = np.stack([vid(ci, cj, ck), vid(ci + 1, cj, ck),
@@ -325,7 +332,8 @@ def build_force_out_csr(mesh: TetrahedralMesh, vertex_loc: np.ndarray):
     flat_v = mesh.tets.reshape(-1)              # index = ele*4 + vtx_id
     order = np.argsort(flat_v, kind="stable")   # MeshVertexReverseList order
     deg = np.bincount(flat_v, minlength=V)
-    assert deg.min() > 0, "dangling vertex"
+    # vertices without tets occur only in a rank's shard of a larger mesh
+    # (make_cuboid(cube_x_range=...)); their rows are empty
     vptr = np.zeros(V + 1, np.int64)
     np.cumsum(deg, out=vptr[1:])
     uv, uc = vertex_loc[:, 0], vertex_loc[:, 1]
