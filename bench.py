@@ -402,10 +402,34 @@ def run_ours(args):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    # whole element phase of a sweep (eval, Jacobian, steps, assembly, comm)
     elem_ms = sum(prof[t][0] for t in ("taylor_next_order", "push_xi",
                                        "remap_out")) / args.steps
     algo = algo_bytes_per_sweep(n_tets, args.energy)
-    achieved = algo / (elem_ms * 1e-3) / 1e9
+    # dominant kernel: the fused order step (coefficient phase k + bias phase
+    # k+1 + assembly), launched for kb = 2..K; algorithmic bytes of launch kb
+    # are B_elem(kb) * tets
+    S = S_MIN[args.energy]
+    step_ms, step_launches = prof["k_fused_step"]
+    if step_launches:
+        step_algo = float(n_tets) * sum(8.0 * (S * (k + 1) + 24)
+                                        for k in range(2, ORDER + 1))
+        kernel_name = "fused.cu StepKernel (order step kb = 2..%d)" % ORDER
+        achieved = step_algo * args.steps / (step_ms * 1e-3) / 1e9
+        bytes_per_launch = step_algo / (ORDER - 1)
+    else:  # generic operator-list path
+        kernel_name = "element kernels of one sweep (generic path)"
+        achieved = algo / (elem_ms * 1e-3) / 1e9
+        bytes_per_launch = None
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles",
+                                         "step_kernel_traffic.json")))
+        if tr.get("energy_model") == args.energy and \
+                tr.get("tets") == int(n_tets):
+            traffic = tr
+    except Exception:
+        pass
     line = {
         "metric": "tet_order_steps_per_s", "value": value,
         "unit": "tet*order/s", "n_gpus": world, "steps": args.steps,
@@ -420,13 +444,19 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": None,
-            "peak_source": ("MEASURED_PEAKS.json hbm_gbs (measured)"
-                            if peaks else "fallback 6650 GB/s"),
-            "kernel": "element order-step kernels of one sweep "
-                      "(bias + coeff phases, gather, assembly)",
-            "algorithmic_bytes_per_sweep": algo,
-            "element_ms_per_sweep": elem_ms,
+            "frac": achieved / peak,
+            "traffic": traffic["dram_bytes"] if traffic else None,
+            "traffic_note": (traffic["note"] if traffic else
+                             "no ncu capture for this configuration"),
+            "peak_source": ("MEASURED_PEAKS.json hbm_gbs (measured copy "
+                            "bandwidth)" if peaks else "fallback 6650 GB/s"),
+            "kernel": kernel_name,
+            "algorithmic_bytes_per_launch_avg": bytes_per_launch,
+            "launch_ms_avg": (step_ms / step_launches if step_launches
+                              else None),
+            "sweep": {"algorithmic_bytes": algo, "element_ms": elem_ms,
+                      "achieved": algo / (elem_ms * 1e-3) / 1e9,
+                      "frac": algo / (elem_ms * 1e-3) / 1e9 / peak},
             "state_doubles_impl": st["state_doubles"],
             "state_doubles_min": S_MIN[args.energy],
             "arena_bytes": st["arena_bytes"],
