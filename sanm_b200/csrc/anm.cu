@@ -1,5 +1,6 @@
 /* sanm_b200/csrc/anm.cu -- see anm.h. */
 #include "anm.h"
+#include "cache.h"
 #include "comm.h"
 #include "shard.h"
 #include "poly.h"
@@ -260,6 +261,13 @@ KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
                (size_t)m_rout->nr_out(), (size_t)n);
     sanm_check(m_rout->nr_in() == batch * odim);
     sanm_check(m_rin->nr_out() == batch * idim);
+    // the pattern depends on the structure of the two maps only
+    static LruCache<const Pattern> cache{6};
+    uint64_t key = m_rin->hash_struct() * 0x9E3779B97F4A7C15ull ^
+                   m_rout->hash_struct();
+    key = hash_bytes(&key, 8, n * 131 + odim * 17 + idim * 3 + elemwise);
+    m_pat = cache.get(key);
+    if (m_pat && m_pat->rowptr.size() == n + 1) return;
     const auto& orp = m_rout->h_rowptr();
     const auto& oix = m_rout->h_idx();
     const auto& irp = m_rin->h_rowptr();
@@ -300,6 +308,9 @@ KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
             rows[r] = cand;
         }
     }
+    auto pat = std::make_shared<Pattern>();
+    auto& m_rowptr = pat->rowptr;
+    auto& m_colidx = pat->colidx;
     m_rowptr.assign(n + 1, 0);
     for (uint64_t r = 0; r < n; ++r) {
         sanm_check(!rows[r].empty(), "empty row %zu", (size_t)r);
@@ -310,14 +321,17 @@ KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
     for (uint64_t r = 0; r < n; ++r) {
         std::copy(rows[r].begin(), rows[r].end(), m_colidx.begin() + m_rowptr[r]);
     }
-    m_d_rowptr.upload(m_rowptr);
-    m_d_colidx.upload(m_colidx);
+    pat->d_rowptr.upload(m_rowptr);
+    pat->d_colidx.upload(m_colidx);
+    pat->hash = hash_vec(m_colidx, hash_vec(m_rowptr, n));
+    m_pat = pat;
+    cache.put(key, m_pat);
 }
 
 void KAssembler::assemble(double* vals, double* grad_t, const double* jac,
                           int64_t jac_pitch) const {
     sanm_check(!jac_pitch || !m_elemwise);
-    rt::for_each(m_n, AssembleK{m_d_rowptr.ptr(), m_d_colidx.ptr(),
+    rt::for_each(m_n, AssembleK{m_pat->d_rowptr.ptr(), m_pat->d_colidx.ptr(),
                                 m_asm_rout->d_rowptr(), m_asm_rout->d_idx(),
                                 m_asm_rout->d_coeff(), m_asm_rin->d_rowptr(),
                                 m_asm_rin->d_idx(), m_asm_rin->d_coeff(), jac,
@@ -554,9 +568,18 @@ void AnmSolver::solve_expansion_coeffs() {
                     m_d_kvals.alloc(m_kasm->nnz());
                     if (fio && m_prop->jacobian_pitch()) {
                         SANM_PROF("K_elem_lists_host");
-                        m_kfused = FusedKAssembly::build(
-                                *m_prop->fused_io(), n, m_kasm->rowptr(),
-                                m_kasm->colidx());
+                        // lists depend on the mesh tables and the pattern
+                        static LruCache<const FusedKAssembly> kcache{6};
+                        const FusedIO& io = *m_prop->fused_io();
+                        uint64_t key = io.hash * 0x9E3779B97F4A7C15ull ^
+                                       m_kasm->pattern_hash();
+                        key = hash_bytes(&key, 8, n);
+                        m_kfused = io.hash ? kcache.get(key) : nullptr;
+                        if (!m_kfused) {
+                            m_kfused = FusedKAssembly::build(
+                                    io, n, m_kasm->rowptr(), m_kasm->colidx());
+                            if (m_kfused && io.hash) kcache.put(key, m_kfused);
+                        }
                     }
                 }
                 SANM_PROF("k_assemble_K");

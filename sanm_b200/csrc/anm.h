@@ -46,9 +46,18 @@ public:
                int odim, int idim, bool elemwise,
                std::shared_ptr<const Remap> asm_rin = nullptr,
                std::shared_ptr<const Remap> asm_rout = nullptr);
-    const std::vector<uint32_t>& rowptr() const { return m_rowptr; }
-    const std::vector<uint32_t>& colidx() const { return m_colidx; }
-    uint64_t nnz() const { return m_colidx.size(); }
+    const std::vector<uint32_t>& rowptr() const { return m_pat->rowptr; }
+    const std::vector<uint32_t>& colidx() const { return m_pat->colidx; }
+    uint64_t nnz() const { return m_pat->colidx.size(); }
+    //! content hash of the pattern (key of the caches that depend on it)
+    uint64_t pattern_hash() const { return m_pat->hash; }
+
+    //! structural pattern of K; shared between solver instances (cache.h)
+    struct Pattern {
+        std::vector<uint32_t> rowptr, colidx;
+        rt::DBuf<uint32_t> d_rowptr, d_colidx;
+        uint64_t hash = 0;
+    };
     //! vals (device, nnz) and grad_t (device, n; may be null) from the
     //! per-item Jacobian (device, [N][odim][idim] or [N][dim]; with
     //! jac_pitch != 0 the FULL form is stored [odim*idim][jac_pitch])
@@ -63,8 +72,7 @@ private:
     uint64_t m_n, m_batch;
     int m_odim, m_idim;
     bool m_elemwise;
-    std::vector<uint32_t> m_rowptr, m_colidx;
-    rt::DBuf<uint32_t> m_d_rowptr, m_d_colidx;
+    std::shared_ptr<const Pattern> m_pat;
 };
 
 //! element-wise K assembly for the mesh remaps of fea (k_assemble.cu)
@@ -145,7 +153,7 @@ private:
 
     std::unique_ptr<TaylorProp> m_prop;
     std::unique_ptr<KAssembler> m_kasm;
-    std::unique_ptr<FusedKAssembly> m_kfused;
+    std::shared_ptr<const FusedKAssembly> m_kfused;
     SparseLU m_lu;
 
     // host state

@@ -31,6 +31,7 @@ namespace sanm_b200 {
 
 struct FusedIO {
     uint64_t n_tets = 0, nin = 0, nout = 0;
+    uint64_t hash = 0;  //!< content hash of the two maps it was derived from
     int64_t npad = 0;
     // ---- gather
     int wu = 0;   //!< unit references per shape-matrix entry (<= 2)

@@ -50,6 +50,8 @@ Remap::Remap(const Shape& out_shape, const Shape& in_shape,
         m_h_idx[i] = (uint32_t)idx[i];
     }
     m_h_coeff.assign(coeff, coeff + nnz);
+    m_hash_struct = hash_vec(m_h_idx, hash_vec(m_h_rowptr, n * 31 + nin));
+    m_hash_full = hash_vec(m_h_coeff, m_hash_struct);
     m_rowptr.upload(m_h_rowptr);
     m_idx.upload(m_h_idx);
     m_coeff.upload(m_h_coeff);

@@ -40,12 +40,16 @@ public:
     const std::vector<uint32_t>& h_rowptr() const { return m_h_rowptr; }
     const std::vector<uint32_t>& h_idx() const { return m_h_idx; }
     const std::vector<double>& h_coeff() const { return m_h_coeff; }
+    //! content hashes: sparsity structure only / structure + coefficients
+    uint64_t hash_struct() const { return m_hash_struct; }
+    uint64_t hash_full() const { return m_hash_full; }
     const uint32_t* d_rowptr() const { return m_rowptr.ptr(); }
     const uint32_t* d_idx() const { return m_idx.ptr(); }
     const double* d_coeff() const { return m_coeff.ptr(); }
 
 private:
     Shape m_out, m_in;
+    uint64_t m_hash_struct = 0, m_hash_full = 0;
     std::vector<uint32_t> m_h_rowptr, m_h_idx;
     std::vector<double> m_h_coeff;
     rt::DBuf<uint32_t> m_rowptr, m_idx;

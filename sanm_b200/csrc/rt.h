@@ -72,6 +72,32 @@ SANM_HD inline void rt_atomic_inc(int* p) {
 #endif
 }
 
+//! 64-bit content hash (splitmix-style mixing of 8-byte words); keys of the
+//! topology caches (symbolic analysis, assembly lists) across solver instances
+inline uint64_t hash_bytes(const void* data, size_t bytes,
+                           uint64_t seed = 0x9E3779B97F4A7C15ull) {
+    const unsigned char* p = static_cast<const unsigned char*>(data);
+    uint64_t h = seed ^ (bytes * 0xBF58476D1CE4E5B9ull);
+    size_t i = 0;
+    for (; i + 8 <= bytes; i += 8) {
+        uint64_t w;
+        memcpy(&w, p + i, 8);
+        h ^= w;
+        h *= 0xBF58476D1CE4E5B9ull;
+        h ^= h >> 29;
+    }
+    uint64_t w = 0;
+    if (i < bytes) memcpy(&w, p + i, bytes - i);
+    h ^= w;
+    h *= 0x94D049BB133111EBull;
+    h ^= h >> 31;
+    return h;
+}
+template <typename T>
+inline uint64_t hash_vec(const std::vector<T>& v, uint64_t seed) {
+    return hash_bytes(v.data(), v.size() * sizeof(T), seed);
+}
+
 namespace rt {
 
 #ifdef SANM_HOSTEMU

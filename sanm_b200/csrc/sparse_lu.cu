@@ -3,6 +3,7 @@
 #include "sparse_lu.h"
 
 #include <cstdlib>
+#include "cache.h"
 #include "sparse_symbolic.h"
 
 #include <algorithm>
@@ -470,7 +471,7 @@ struct SpmvKernel {
 }  // namespace
 
 struct SparseLU::Impl {
-    Symbolic sym;
+    std::shared_ptr<const Symbolic> sym;
     std::vector<uint32_t> h_rowptr, h_colidx;
     rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list, rowperm;
     rt::DBuf<int32_t> inv;
@@ -508,8 +509,21 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     m_nnz = rowptr[n];
     I.h_rowptr.assign(rowptr, rowptr + n + 1);
     I.h_colidx.assign(colidx, colidx + m_nnz);
-    I.sym = symbolic_analyze((uint32_t)n, rowptr, colidx);
-    const Symbolic& S = I.sym;
+    {
+        // the symbolic analysis depends on the pattern only: shared between
+        // solver instances (ANM iterations re-use one instance anyway; chained
+        // stages of a run create new ones)
+        static LruCache<const Symbolic> cache{6};
+        const uint64_t key = hash_vec(
+                I.h_colidx, hash_vec(I.h_rowptr, n * 0x51ED27ull + m_nnz));
+        I.sym = cache.get(key);
+        if (!I.sym || I.sym->n != n || I.sym->a_dest.size() != m_nnz) {
+            I.sym = std::make_shared<const Symbolic>(
+                    symbolic_analyze((uint32_t)n, rowptr, colidx));
+            cache.put(key, I.sym);
+        }
+    }
+    const Symbolic& S = *I.sym;
 
     I.rowptr.upload(I.h_rowptr);
     I.colidx.upload(I.h_colidx);

@@ -1,6 +1,7 @@
 /* sanm_b200/csrc/taylor.cu -- see taylor.h.  Kernels: one thread per batch item
  * (tetrahedron), walking the lowered operator list (taylor_dev.h). */
 #include "taylor.h"
+#include "cache.h"
 #include "prof.h"
 #include "remap.h"
 
@@ -335,8 +336,19 @@ bool TaylorProp::attach_io(const Remap& rin, const Remap& rout) {
     if (m_fused->has_io()) return true;
     const char* off = getenv("SANM_NO_FUSED_IO");
     if (off && off[0] == '1') return false;
-    std::shared_ptr<const FusedIO> io = FusedIO::analyse(rin, rout, m_low.batch);
-    if (!io) return false;
+    // derived tables depend on the two maps only: shared between solver
+    // instances over the same mesh (cache.h)
+    static LruCache<const FusedIO> cache{6};
+    uint64_t key = rin.hash_full() * 0x9E3779B97F4A7C15ull ^ rout.hash_full();
+    key = hash_bytes(&key, 8, m_low.batch);
+    std::shared_ptr<const FusedIO> io = cache.get(key);
+    if (!io || io->n_tets != m_low.batch) {
+        std::unique_ptr<FusedIO> fresh = FusedIO::analyse(rin, rout, m_low.batch);
+        if (!fresh) return false;
+        fresh->hash = key;
+        io = std::move(fresh);
+        cache.put(key, io);
+    }
     m_fused->attach_io(std::move(io));
     return true;
 }
