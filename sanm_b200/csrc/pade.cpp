@@ -3,15 +3,33 @@
 #include "poly.h"
 #include "rt.h"
 
+#include <algorithm>
 #include <cmath>
+#include <vector>
 #include <limits>
 
 namespace sanm_b200 {
 
 namespace {
+//! fixed chunking => the result does not depend on the number of threads
 double dot(const double* a, const double* b, size_t n) {
+    constexpr size_t CHUNK = 4096;
+    const size_t nchunk = (n + CHUNK - 1) / CHUNK;
+    if (nchunk <= 1) {
+        double s = 0;
+        for (size_t i = 0; i < n; ++i) s += a[i] * b[i];
+        return s;
+    }
+    std::vector<double> part(nchunk);
+#pragma omp parallel for schedule(static)
+    for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
+        const size_t i0 = c * CHUNK, i1 = std::min(n, i0 + CHUNK);
+        double s = 0;
+        for (size_t i = i0; i < i1; ++i) s += a[i] * b[i];
+        part[c] = s;
+    }
     double s = 0;
-    for (size_t i = 0; i < n; ++i) s += a[i] * b[i];
+    for (double v : part) s += v;
     return s;
 }
 }  // namespace
@@ -40,7 +58,8 @@ PadeApproximation::PadeApproximation(std::vector<const double*> xs, size_t len,
             } else {
                 const double f = -a(i, j);
                 const double* o = orth[j].data();
-                for (size_t q = 0; q < len; ++q) u[q] += o[q] * f;
+#pragma omp parallel for schedule(static)
+                for (int64_t q = 0; q < (int64_t)len; ++q) u[q] += o[q] * f;
             }
         }
         double aii = std::sqrt(dot(u.data(), u.data(), len));
@@ -96,7 +115,10 @@ std::vector<double> PadeApproximation::eval_nume(double a, const double* d,
     for (int i = n; i >= 1; --i) {
         double scale = poly::eval(d, n - i + 1, a);
         const double* x = m_xs[i];
-        for (size_t q = 0; q < m_len; ++q) sum[q] = sum[q] * a + x[q] * scale;
+#pragma omp parallel for schedule(static)
+        for (int64_t q = 0; q < (int64_t)m_len; ++q) {
+            sum[q] = sum[q] * a + x[q] * scale;
+        }
     }
     return sum;
 }
@@ -126,12 +148,12 @@ bool PadeApproximation::estimate_valid_range(double start, double eps,
         std::vector<double> pn = eval_nume(a, m_d.data(), n),
                             pl = eval_nume(a, m_d_lo.data(), n - 1);
         const double f = denom_n / denom_lo;
-        double diff2 = 0, pn2 = 0;
-        for (size_t q = 0; q < m_len; ++q) {
-            double v = pl[q] * f - pn[q];
-            diff2 += v * v;
-            pn2 += pn[q] * pn[q];
-        }
+        // same fixed chunking as dot()
+        std::vector<double> dv(m_len);
+#pragma omp parallel for schedule(static)
+        for (int64_t q = 0; q < (int64_t)m_len; ++q) dv[q] = pl[q] * f - pn[q];
+        const double diff2 = dot(dv.data(), dv.data(), m_len),
+                     pn2 = dot(pn.data(), pn.data(), m_len);
         return diff2 <= pn2 * eps2;
     };
     double left = start * 1.001, right = start + (pole - start) * 0.99;

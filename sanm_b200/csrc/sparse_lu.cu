@@ -16,6 +16,7 @@ namespace {
 constexpr int NB = 32;          //!< pivot block of the large-front path
 constexpr uint32_t SMALL_NR = 104;  //!< fronts up to this size live in smem
 constexpr int ASM_TILE = 4096;  //!< entries per assembly task
+constexpr int ABSMAX_BLOCKS = 256;
 
 struct FrontD {
     double* F;        //!< nr x nr, column-major
@@ -23,6 +24,7 @@ struct FrontD {
     const uint32_t* st;  //!< row structure (permuted indices)
     const int32_t* inv;  //!< map parent row -> own update row (size nr_parent)
     uint32_t* rowperm;   //!< [nc] row permutation of the pivot block
+    uint32_t* lperm;     //!< [NB] row permutation of the current pivot step
     uint32_t nr, nc, c0;
     uint32_t child_begin, child_end;
     int32_t parent;
@@ -43,12 +45,14 @@ struct ScatterA {
 
 struct AbsMaxKernel {
     const double* v;
-    uint64_t n;
-    double* out;  // out[0] = max |v|
+    uint64_t n, nblk;
+    double* out;  // out[bid] = max |v| over the block's share
     SANM_D void operator()(const rt::BlockCtx& c) const {
         double* red = reinterpret_cast<double*>(c.smem);
         double m = 0;
-        for (uint64_t i = c.tid; i < n; i += c.nthr) {
+        const uint64_t per = (n + nblk - 1) / nblk;
+        const uint64_t i0 = c.bid * per, i1 = i0 + per < n ? i0 + per : n;
+        for (uint64_t i = i0 + c.tid; i < i1; i += c.nthr) {
             double a = fabs(v[i]);
             m = a > m ? a : m;
         }
@@ -58,7 +62,7 @@ struct AbsMaxKernel {
             if (c.tid < s) red[c.tid] = red[c.tid] > red[c.tid + s] ? red[c.tid] : red[c.tid + s];
             c.sync();
         }
-        if (c.tid == 0) out[0] = red[0];
+        if (c.tid == 0) out[c.bid] = red[0];
     }
 };
 
@@ -74,7 +78,8 @@ struct AssembleChildren {
         const uint64_t e0 = (uint64_t)tk.chunk * ASM_TILE;
         const uint64_t e1 = e0 + ASM_TILE < total ? e0 + ASM_TILE : total;
         for (uint64_t e = e0 + c.tid; e < e1; e += c.nthr) {
-            const uint32_t i = (uint32_t)(e % f.nr), j = (uint32_t)(e / f.nr);
+            const uint32_t e32 = (uint32_t)e;  // nr <= 13000: fits
+            const uint32_t i = e32 % f.nr, j = e32 / f.nr;
             double acc = 0;
             for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
                 const FrontD ch = fronts[child_list[q]];
@@ -136,9 +141,10 @@ SANM_D inline void gj_steps(const rt::BlockCtx& c, double* M, uint32_t ld,
             if (j != k) M[(uint64_t)j * ld + k] *= ip;
         }
         c.sync();
-        const uint64_t tot = (uint64_t)m * m;
-        for (uint64_t e = c.tid; e < tot; e += c.nthr) {
-            const uint32_t i = (uint32_t)(e % m), j = (uint32_t)(e / m);
+        // 32-bit index arithmetic: m <= 13000, and 64-bit division is slow
+        const uint32_t tot = m * m;
+        for (uint32_t e = c.tid; e < tot; e += c.nthr) {
+            const uint32_t i = e % m, j = e / m;
             if (i != k && j != k) {
                 M[(uint64_t)j * ld + i] -= M[(uint64_t)k * ld + i] * M[(uint64_t)j * ld + k];
             }
@@ -204,15 +210,9 @@ struct BigDiagKernel {
             uint32_t i = e % nb, j = e / nb;
             f.F[(uint64_t)(kb + j) * f.nr + kb + i] = D[j * NB + i];
         }
-        // row i of the block now holds original row lperm[i]: permute the rest
-        // of the block row accordingly (columns outside the diagonal block)
-        for (uint32_t j = c.tid; j < f.nr; j += c.nthr) {
-            if (j >= kb && j < kb + nb) continue;
-            double* col = f.F + (uint64_t)j * f.nr + kb;
-            double tmp[NB];
-            for (uint32_t i = 0; i < nb; ++i) tmp[i] = col[lperm[i]];
-            for (uint32_t i = 0; i < nb; ++i) col[i] = tmp[i];
-        }
+        // row i of the block now holds original row lperm[i]; the rest of
+        // the block row is permuted by BigRowPanelKernel while it loads it
+        for (uint32_t i = c.tid; i < nb; i += c.nthr) f.lperm[i] = lperm[i];
         c.sync();
         if (c.tid == 0) {
             uint32_t tmp[NB];
@@ -240,9 +240,10 @@ struct BigRowPanelKernel {
             uint32_t i = e % nb, j = e / nb;
             Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
         }
+        // rows of the pivot block were swapped by BigDiagKernel (lperm)
         for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
             uint32_t i = e % nb, j = e / nb;
-            R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + i];
+            R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + f.lperm[i]];
         }
         c.sync();
         for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
@@ -350,10 +351,14 @@ struct BigColPanelKernel {
  * order through shared memory, so results are bitwise reproducible and a
  * dense front of any size spreads over nr/32 blocks x 8 warps. */
 constexpr int SOLVE_ROWS = 32;
-constexpr int SOLVE_WARPS = 8;
-constexpr int SOLVE_THREADS = SOLVE_ROWS * SOLVE_WARPS;
+//! column groups per block: 8 for levels of small fronts, 32 where a front has
+//! many columns (the sequential chain of L2-latency-bound loads per lane is
+//! what bounds a level, so wide fronts get more groups)
+constexpr int SOLVE_WARPS_NARROW = 8, SOLVE_WARPS_WIDE = 32;
+constexpr uint32_t SOLVE_WIDE_COLS = 192;
 
 //! partial dot products of rows [r0, r0+32) of a column-major block with v
+template <int SOLVE_WARPS>
 SANM_HD inline double solve_partial(const double* col0, uint64_t ld,
                                     uint32_t ncol, const double* v, int g) {
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
@@ -370,7 +375,9 @@ SANM_HD inline double solve_partial(const double* col0, uint64_t ld,
 
 //! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates;
 //! b is read through the fill-reducing permutation
+template <int SOLVE_WARPS>
 struct ForwardKernel {
+    static constexpr int SOLVE_THREADS = SOLVE_ROWS * SOLVE_WARPS;
     const FrontD* fronts;
     const uint32_t* child_list;
     const Task* tasks;
@@ -402,7 +409,7 @@ struct ForwardKernel {
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
             const uint32_t r = r0 + lane;
-            part[th] = r < nu ? solve_partial(f.F + f.nc + r, f.nr, f.nc, w1p, g)
+            part[th] = r < nu ? solve_partial<SOLVE_WARPS>(f.F + f.nc + r, f.nr, f.nc, w1p, g)
                               : 0.0;
         }
         c.sync();
@@ -423,7 +430,9 @@ struct ForwardKernel {
 
 //! backward: x1 = G w1' - F12' x2, written to the permuted work vector (read
 //! by descendants) and to the caller's vector in original numbering
+template <int SOLVE_WARPS>
 struct BackwardKernel {
+    static constexpr int SOLVE_THREADS = SOLVE_ROWS * SOLVE_WARPS;
     const FrontD* fronts;
     const Task* tasks;
     double* xp;  // permuted solution
@@ -441,7 +450,7 @@ struct BackwardKernel {
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
             const uint32_t r = r0 + lane;
-            part[th] = r < f.nc ? solve_partial(f.F + r, f.nr, f.nr, v, g) : 0.0;
+            part[th] = r < f.nc ? solve_partial<SOLVE_WARPS>(f.F + r, f.nr, f.nr, v, g) : 0.0;
         }
         c.sync();
         for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
@@ -473,7 +482,7 @@ struct SpmvKernel {
 struct SparseLU::Impl {
     std::shared_ptr<const Symbolic> sym;
     std::vector<uint32_t> h_rowptr, h_colidx;
-    rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list, rowperm;
+    rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list, rowperm, lperm;
     rt::DBuf<int32_t> inv;
     rt::DBuf<uint64_t> a_dest;
     rt::DBuf<double> fronts, vecs, vals, bp, xp, scal;
@@ -535,10 +544,11 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.fronts.alloc(S.front_total);
     I.vecs.alloc(S.soff[S.nsn]);
     I.rowperm.alloc(n);
+    I.lperm.alloc((size_t)S.nsn * NB);
     I.vals.alloc(m_nnz);
     I.bp.alloc(n);
     I.xp.alloc(n);
-    I.scal.alloc(4);
+    I.scal.alloc(4 + ABSMAX_BLOCKS);
     I.counters.alloc(4);
     I.counters.zero();
 
@@ -551,6 +561,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         f.st = I.structs.ptr() + S.soff[s];
         f.inv = S.sn_parent[s] >= 0 ? I.inv.ptr() + S.inv_off[s] : nullptr;
         f.rowperm = I.rowperm.ptr() + S.sn_c0[s];
+        f.lperm = I.lperm.ptr() + (size_t)s * NB;
         f.nr = S.sn_nr[s];
         f.nc = S.sn_nc[s];
         f.c0 = S.sn_c0[s];
@@ -653,8 +664,13 @@ void SparseLU::factor(const double* vals_dev) {
     }
     I.fronts.zero();
     I.counters.zero();
+    // max |a_ij| (scale of the static pivot threshold): two stages
+    rt::for_each_block(ABSMAX_BLOCKS, 256, 256 * sizeof(double),
+                       AbsMaxKernel{I.vals.ptr(), m_nnz, ABSMAX_BLOCKS,
+                                    I.scal.ptr() + 4});
     rt::for_each_block(1, 256, 256 * sizeof(double),
-                       AbsMaxKernel{I.vals.ptr(), m_nnz, I.scal.ptr()});
+                       AbsMaxKernel{I.scal.ptr() + 4, ABSMAX_BLOCKS, 1,
+                                    I.scal.ptr()});
     rt::for_each(m_nnz, ScatterA{I.fronts.ptr(), I.a_dest.ptr(), I.vals.ptr()});
     const double* amax = I.scal.ptr();
     int* npert = I.counters.ptr();
@@ -700,20 +716,41 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
     // b may alias x: the forward sweep has consumed b before the backward
     // sweep writes x
     for (auto& L : I.levels) {
-        rt::for_each_block(
-                L.fwd_n, SOLVE_THREADS,
-                (2 * (size_t)L.max_nc + SOLVE_THREADS) * sizeof(double),
-                ForwardKernel{I.fd.ptr(), I.child_list.ptr(),
-                              I.fwd_tasks.ptr() + L.fwd_off, b_dev,
-                              I.perm.ptr()});
+        if (L.max_nc >= SOLVE_WIDE_COLS) {
+            constexpr int W = SOLVE_WARPS_WIDE;
+            rt::for_each_block(
+                    L.fwd_n, SOLVE_ROWS * W,
+                    (2 * (size_t)L.max_nc + SOLVE_ROWS * W) * sizeof(double),
+                    ForwardKernel<W>{I.fd.ptr(), I.child_list.ptr(),
+                                     I.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                     I.perm.ptr()});
+        } else {
+            constexpr int W = SOLVE_WARPS_NARROW;
+            rt::for_each_block(
+                    L.fwd_n, SOLVE_ROWS * W,
+                    (2 * (size_t)L.max_nc + SOLVE_ROWS * W) * sizeof(double),
+                    ForwardKernel<W>{I.fd.ptr(), I.child_list.ptr(),
+                                     I.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                     I.perm.ptr()});
+        }
     }
     for (size_t l = I.levels.size(); l-- > 0;) {
         auto& L = I.levels[l];
-        rt::for_each_block(
-                L.bwd_n, SOLVE_THREADS,
-                ((size_t)L.max_nr + SOLVE_THREADS) * sizeof(double),
-                BackwardKernel{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
-                               I.xp.ptr(), x_dev, I.perm.ptr()});
+        if (L.max_nr >= SOLVE_WIDE_COLS) {
+            constexpr int W = SOLVE_WARPS_WIDE;
+            rt::for_each_block(
+                    L.bwd_n, SOLVE_ROWS * W,
+                    ((size_t)L.max_nr + SOLVE_ROWS * W) * sizeof(double),
+                    BackwardKernel<W>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
+                                      I.xp.ptr(), x_dev, I.perm.ptr()});
+        } else {
+            constexpr int W = SOLVE_WARPS_NARROW;
+            rt::for_each_block(
+                    L.bwd_n, SOLVE_ROWS * W,
+                    ((size_t)L.max_nr + SOLVE_ROWS * W) * sizeof(double),
+                    BackwardKernel<W>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
+                                      I.xp.ptr(), x_dev, I.perm.ptr()});
+        }
     }
 }
 
