@@ -368,16 +368,18 @@ def run_ours(args):
     clocks = sampler.stop()
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region
-    sweep.set_x(x_host)
-    sweep.run()
-    sweep.get_b(b_host)
+    # (sanm_sweep_run_host: x_k uploaded / b_k downloaded on two copy streams
+    # while other orders are being propagated)
+    b_host[:] = 0
+    sweep.run_host(x_host, b_host)
+    b_check = sweep.get_b()
+    assert np.array_equal(b_check, b_host), "pipelined e2e result differs"
+    del b_check
     barrier()
     ev2, ev3 = torch.cuda.Event(True), torch.cuda.Event(True)
     ev2.record(stream)
     for _ in range(args.steps):
-        sweep.set_x(x_host)
-        sweep.run()
-        sweep.get_b(b_host)
+        sweep.run_host(x_host, b_host)
     ev3.record(stream)
     barrier()
     ms_e2e = ev2.elapsed_time(ev3)

@@ -178,6 +178,11 @@ int sanm_sweep_destroy(sanm_sweep_t* s);
 int sanm_sweep_set_x(sanm_sweep_t* s, const double* x);
 /* one full sweep over orders 0..K on the device (asynchronous) */
 int sanm_sweep_run(sanm_sweep_t* s);
+/* set_x + run + get_b in one call with HOST buffers (pinned for overlap): x_k
+ * is uploaded while earlier orders are propagated and b_k is downloaded as
+ * soon as order k has been assembled (two copy streams beside the compute
+ * stream); returns when b has arrived.  Same results as the three calls. */
+int sanm_sweep_run_host(sanm_sweep_t* s, const double* x, double* b);
 /* b: host [(order+1), n_out] (rows b_0..b_K); synchronises */
 int sanm_sweep_get_b(sanm_sweep_t* s, double* b);
 /* tet*order steps of one sweep, algorithmic HBM bytes of one sweep (SURVEY 8d:

@@ -76,6 +76,11 @@ def _ptr(a: np.ndarray):
     return a.ctypes.data_as(_dp)
 
 
+import os as _os
+import time as _time
+_TRACE_CALLS = bool(_os.environ.get("SANM_TRACE_CALLS"))
+
+
 class Binding:
     """All entry points of one implementation (``sanm_`` or ``ref_``)."""
 
@@ -92,8 +97,19 @@ class Binding:
     def has(self, name) -> bool:
         return hasattr(self.lib, self.prefix + name)
 
+    #: host wall time per entry point when SANM_TRACE_CALLS is set (a
+    #: measurement aid for tools/solve_profile.py; off by default)
+    call_times: dict = {}
+
     def call(self, name, *args):
-        st = self.fn(name)(*args)
+        if _TRACE_CALLS:
+            t0 = _time.perf_counter()
+            st = self.fn(name)(*args)
+            rec = Binding.call_times.setdefault(self.prefix + name, [0.0, 0])
+            rec[0] += _time.perf_counter() - t0
+            rec[1] += 1
+        else:
+            st = self.fn(name)(*args)
         if st != 0:
             msg = self._last_error().decode(errors="replace")
             raise _ERRS.get(st, SANMError)(msg)
@@ -598,6 +614,16 @@ class ElementSweep:
         if out is None:
             out = np.empty((self.order + 1, self.n_out))
         self.b.call("sweep_get_b", self.h, _ptr(out))
+        return out
+
+    def run_host(self, x, out=None) -> np.ndarray:
+        """set_x + run + get_b with the copies overlapped (host buffers)"""
+        x = _f64(x)
+        assert x.shape == (self.order + 1, self.n_in)
+        if out is None:
+            out = np.empty((self.order + 1, self.n_out))
+        assert out.dtype == np.float64 and out.flags.c_contiguous
+        self.b.call("sweep_run_host", self.h, _ptr(x), _ptr(out))
         return out
 
     def stats(self):

@@ -28,6 +28,13 @@ void h2d(void* dst, const void* src, size_t bytes) { memcpy(dst, src, bytes); }
 void d2h(void* dst, const void* src, size_t bytes) { memcpy(dst, src, bytes); }
 void d2d(void* dst, const void* src, size_t bytes) { memmove(dst, src, bytes); }
 void dzero(void* dst, size_t bytes) { memset(dst, 0, bytes); }
+void pipe_h2d(void* dst, const void* src, size_t bytes) { memcpy(dst, src, bytes); }
+void pipe_d2h(void* dst, const void* src, size_t bytes) { memcpy(dst, src, bytes); }
+void* fence_main() { return nullptr; }
+void* fence_pipe(int) { return nullptr; }
+void main_wait(void*) {}
+void pipe_wait(int, void*) {}
+void pipe_sync(int) {}
 void* hmalloc_pinned(size_t bytes) { return malloc(bytes ? bytes : 1); }
 void hfree_pinned(void* p) { free(p); }
 
@@ -100,6 +107,44 @@ void d2d(void* dst, const void* src, size_t bytes) {
 void dzero(void* dst, size_t bytes) {
     SANM_CUDA_CHECK(cudaMemsetAsync(dst, 0, bytes, stream()));
 }
+
+namespace {
+cudaStream_t g_pipe[2] = {nullptr, nullptr};
+cudaStream_t pipe_stream(int pipe) {
+    check_device();
+    if (!g_pipe[pipe]) {
+        SANM_CUDA_CHECK(cudaStreamCreateWithFlags(&g_pipe[pipe], cudaStreamNonBlocking));
+    }
+    return g_pipe[pipe];
+}
+void* fence_on(cudaStream_t s) {
+    cudaEvent_t ev;
+    SANM_CUDA_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    SANM_CUDA_CHECK(cudaEventRecord(ev, s));
+    return ev;
+}
+void wait_on(cudaStream_t s, void* fence) {
+    cudaEvent_t ev = static_cast<cudaEvent_t>(fence);
+    SANM_CUDA_CHECK(cudaStreamWaitEvent(s, ev, 0));
+    // the wait has been queued; the event's resources are released by the
+    // runtime once it has completed
+    SANM_CUDA_CHECK(cudaEventDestroy(ev));
+}
+}  // namespace
+
+void pipe_h2d(void* dst, const void* src, size_t bytes) {
+    SANM_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice,
+                                    pipe_stream(PIPE_H2D)));
+}
+void pipe_d2h(void* dst, const void* src, size_t bytes) {
+    SANM_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost,
+                                    pipe_stream(PIPE_D2H)));
+}
+void* fence_main() { return fence_on(stream()); }
+void* fence_pipe(int pipe) { return fence_on(pipe_stream(pipe)); }
+void main_wait(void* fence) { wait_on(stream(), fence); }
+void pipe_wait(int pipe, void* fence) { wait_on(pipe_stream(pipe), fence); }
+void pipe_sync(int pipe) { SANM_CUDA_CHECK(cudaStreamSynchronize(pipe_stream(pipe))); }
 
 void* hmalloc_pinned(size_t bytes) {
     check_device();

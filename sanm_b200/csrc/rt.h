@@ -132,6 +132,19 @@ void h2d(void* dst, const void* src, size_t bytes);
 void d2h(void* dst, const void* src, size_t bytes);
 void d2d(void* dst, const void* src, size_t bytes);
 void dzero(void* dst, size_t bytes);
+/* Copy pipes: two extra streams (0: host->device, 1: device->host) so that
+ * transfers of one order overlap the element kernels of another.  Ordering is
+ * expressed with fences: a fence taken on one stream can be awaited by the
+ * other without blocking the host. */
+constexpr int PIPE_H2D = 0, PIPE_D2H = 1;
+void pipe_h2d(void* dst, const void* src, size_t bytes);  //!< async on pipe 0
+void pipe_d2h(void* dst, const void* src, size_t bytes);  //!< async on pipe 1
+//! opaque fence = everything queued so far on the main stream / on a pipe
+void* fence_main();
+void* fence_pipe(int pipe);
+void main_wait(void* fence);           //!< main stream waits; consumes the fence
+void pipe_wait(int pipe, void* fence); //!< pipe waits; consumes the fence
+void pipe_sync(int pipe);              //!< host waits for the pipe
 //! pinned host staging memory (plain malloc in the host build)
 void* hmalloc_pinned(size_t bytes);
 void hfree_pinned(void* p);

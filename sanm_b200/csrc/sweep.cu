@@ -32,6 +32,53 @@ public:
     }
 
     void run() {
+        run_impl([](int) {}, [](int) {});
+    }
+
+    /*! One sweep with HOST buffers, transfers overlapped with the element
+     * kernels: x_k travels on the host->device pipe while earlier orders are
+     * being propagated (order k only needs x_0..x_k), b_k leaves on the
+     * device->host pipe as soon as order k has been assembled.  Returns when
+     * b has arrived.  x and b should be pinned for the copies to overlap. */
+    void run_host(const double* x, double* b) {
+        const int K = m_order;
+        // kernels of an earlier sweep may still be reading m_x
+        rt::pipe_wait(rt::PIPE_H2D, rt::fence_main());
+        std::vector<void*> arrived(K + 1, nullptr);
+        for (int k = 0; k <= K; ++k) {
+            rt::pipe_h2d(m_x.ptr() + (size_t)k * m_nin, x + (size_t)k * m_nin,
+                         m_nin * sizeof(double));
+            // x_K is never pushed (libsanm/anm.cpp:205-290: the last order
+            // only produces its bias), but it is part of the caller's series
+            arrived[k] = rt::fence_pipe(rt::PIPE_H2D);
+        }
+        run_impl(
+                [&](int k) {
+                    rt::main_wait(arrived[k]);
+                    arrived[k] = nullptr;
+                },
+                [&](int k) {
+                    rt::pipe_wait(rt::PIPE_D2H, rt::fence_main());
+                    rt::pipe_d2h(b + (size_t)k * m_nout,
+                                 m_b.ptr() + (size_t)k * m_nout,
+                                 m_nout * sizeof(double));
+                });
+        // x_K: nothing on the main stream waits for it; keep stream order sane
+        for (void*& f : arrived) {
+            if (f) {
+                rt::main_wait(f);
+                f = nullptr;
+            }
+        }
+        rt::pipe_sync(rt::PIPE_D2H);
+        rt::sync();
+        m_prop->check_device_error();
+    }
+
+private:
+    //! before_x(k): x_k is about to be read; after_b(k): b_k is complete
+    template <typename BeforeX, typename AfterB>
+    void run_impl(BeforeX&& before_x, AfterB&& after_b) {
         const int K = m_order;
         TaylorProp& p = *m_prop;
         p.reset();
@@ -39,8 +86,10 @@ public:
             // gather and assembly inside the element kernels
             {
                 SANM_PROF("push_xi");
+                before_x(0);
                 p.push_xi_from(m_x.ptr(), m_b.ptr());
                 comm::allreduce_sum(m_b.ptr(), m_nout);
+                after_b(0);
             }
             for (int k = 1; k <= K; ++k) {
                 {
@@ -50,9 +99,11 @@ public:
                     // first compute_next_order_bias (libsanm/symbolic.cpp:249-252)
                     if (k == 1) p.ensure_jacobian();
                     comm::allreduce_sum(m_b.ptr() + (size_t)k * m_nout, m_nout);
+                    after_b(k);
                 }
                 if (k < K) {
                     SANM_PROF("push_xi");
+                    before_x(k);
                     p.push_xi_from(m_x.ptr() + (size_t)k * m_nin);
                 }
             }
@@ -62,6 +113,7 @@ public:
         const VecLayout soa_out{p.out_elems(), p.npad()};
         {
             SANM_PROF("push_xi");
+            before_x(0);
             m_rin->apply(p.input_slot(0), soa_in, m_x.ptr(), VecLayout{});
             p.push_xi_filled();
         }
@@ -69,6 +121,7 @@ public:
             SANM_PROF("remap_out");
             m_rout->apply(m_b.ptr(), VecLayout{}, p.output_slot(0), soa_out);
             comm::allreduce_sum(m_b.ptr(), m_nout);
+            after_b(0);
         }
         for (int k = 1; k <= K; ++k) {
             {
@@ -80,9 +133,11 @@ public:
                 m_rout->apply(m_b.ptr() + (size_t)k * m_nout, VecLayout{},
                               p.output_slot(k), soa_out);
                 comm::allreduce_sum(m_b.ptr() + (size_t)k * m_nout, m_nout);
+                after_b(k);
             }
             if (k < K) {
                 SANM_PROF("push_xi");
+                before_x(k);
                 m_rin->apply(p.input_slot(k), soa_in,
                              m_x.ptr() + (size_t)k * m_nin, VecLayout{});
                 p.push_xi_filled();
@@ -90,6 +145,7 @@ public:
         }
     }
 
+public:
     void get_b(double* b) {
         rt::d2h(b, m_b.ptr(), m_b.size() * sizeof(double));
         m_prop->check_device_error();
@@ -144,6 +200,9 @@ int sanm_sweep_set_x(sanm_sweep_t* s, const double* x) {
 }
 int sanm_sweep_run(sanm_sweep_t* s) {
     return capi::guard([&] { s->s->run(); });
+}
+int sanm_sweep_run_host(sanm_sweep_t* s, const double* x, double* b) {
+    return capi::guard([&] { s->s->run_host(x, b); });
 }
 int sanm_sweep_get_b(sanm_sweep_t* s, double* b) {
     return capi::guard([&] { s->s->get_b(b); });

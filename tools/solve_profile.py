@@ -24,6 +24,14 @@ def main():
         res = fea.run_task(b, task, ovs, save=False,
                            log=fea.RunLog(verbose=False))
         wall = time.perf_counter() - t0
+        if rep == 0 and os.environ.get("SANM_PROFILE_COLD"):
+            print("---- cold run: wall_s", wall)
+            print(b.prof_dump())
+            from sanm_b200.capi import Binding
+            for k, (t, n) in sorted(Binding.call_times.items(),
+                                    key=lambda kv: -kv[1][0])[:12]:
+                print("  call %-34s %9.2f ms  n=%d" % (k, t * 1e3, n))
+            Binding.call_times.clear()
     st = res[1]
     print("wall_s", wall)
     print("stats", st if not isinstance(st, list) else
