@@ -57,6 +57,19 @@ void check_device() {
                                                 : "no device found")};
     }
     SANM_CUDA_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+    {
+        // device memory comes from the stream-ordered pool and stays cached in
+        // it: solvers are created and destroyed once per ANM iteration
+        // (libsanm/anm.cpp:205), cudaMalloc/cudaFree of their 0.1-1 GB buffers
+        // would cost 1-100 ms each time
+        int dev = 0;
+        SANM_CUDA_CHECK(cudaGetDevice(&dev));
+        cudaMemPool_t pool;
+        SANM_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, dev));
+        uint64_t keep = UINT64_MAX;
+        SANM_CUDA_CHECK(cudaMemPoolSetAttribute(
+                pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     g_device_ok = true;
 }
 
@@ -78,12 +91,15 @@ void sync() { SANM_CUDA_CHECK(cudaStreamSynchronize(stream())); }
 void* dmalloc(size_t bytes) {
     check_device();
     void* p = nullptr;
-    SANM_CUDA_CHECK(cudaMalloc(&p, bytes ? bytes : 1));
+    SANM_CUDA_CHECK(cudaMallocAsync(&p, bytes ? bytes : 1, stream()));
     return p;
 }
 
 void dfree(void* p) {
-    if (p) cudaFree(p);
+    // stream-ordered: kernels queued on the library stream that still use p
+    // run before the memory is handed out again (the copy pipes are fenced
+    // against the main stream before their buffers can be released)
+    if (p) cudaFreeAsync(p, g_device_ok ? stream() : nullptr);
 }
 
 void h2d(void* dst, const void* src, size_t bytes) {

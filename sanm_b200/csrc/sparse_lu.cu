@@ -5,6 +5,9 @@
 #include <cstdlib>
 #include "cache.h"
 #include "sparse_symbolic.h"
+#ifndef SANM_HOSTEMU
+#include "gj32.cuh"
+#endif
 
 #include <algorithm>
 #include <cmath>
@@ -103,6 +106,36 @@ SANM_D inline void gj_steps(const rt::BlockCtx& c, double* M, uint32_t ld,
                             uint32_t* rowperm, int* sh, double thresh,
                             int* nr_perturbed) {
     for (uint32_t k = k0; k < k0 + nb; ++k) {
+#ifndef SANM_HOSTEMU
+        if (c.tid < 32) {
+            // warp 0: arg max of |M[i,k]| over i in [k, plim), ties -> lowest i
+            double best = -1.0;
+            uint32_t r = k;
+            for (uint32_t i = k + c.tid; i < plim; i += 32) {
+                double a = fabs(M[(uint64_t)k * ld + i]);
+                if (a > best) {
+                    best = a;
+                    r = i;
+                }
+            }
+            for (int off = 16; off > 0; off >>= 1) {
+                double ob = __shfl_xor_sync(0xffffffffu, best, off);
+                uint32_t orr = __shfl_xor_sync(0xffffffffu, r, off);
+                if (ob > best || (ob == best && orr < r)) {
+                    best = ob;
+                    r = orr;
+                }
+            }
+            if (c.tid == 0) {
+                if (!(best > thresh)) {
+                    double p = M[(uint64_t)k * ld + r];
+                    M[(uint64_t)k * ld + r] = p < 0 ? -thresh : thresh;
+                    rt_atomic_inc(nr_perturbed);
+                }
+                *sh = (int)r;
+            }
+        }
+#else
         if (c.tid == 0) {
             uint32_t r = k;
             double best = fabs(M[(uint64_t)k * ld + k]);
@@ -121,6 +154,7 @@ SANM_D inline void gj_steps(const rt::BlockCtx& c, double* M, uint32_t ld,
             }
             *sh = (int)r;
         }
+#endif
         c.sync();
         const uint32_t r = (uint32_t)*sh;
         if (r != k) {
@@ -141,12 +175,18 @@ SANM_D inline void gj_steps(const rt::BlockCtx& c, double* M, uint32_t ld,
             if (j != k) M[(uint64_t)j * ld + k] *= ip;
         }
         c.sync();
-        // 32-bit index arithmetic: m <= 13000, and 64-bit division is slow
-        const uint32_t tot = m * m;
-        for (uint32_t e = c.tid; e < tot; e += c.nthr) {
-            const uint32_t i = e % m, j = e / m;
-            if (i != k && j != k) {
-                M[(uint64_t)j * ld + i] -= M[(uint64_t)k * ld + i] * M[(uint64_t)j * ld + k];
+        {
+            // warp w takes columns w, w + nw, ...; lanes run down the column
+            const uint32_t wl = c.nthr >= 32 ? 32u : (uint32_t)c.nthr;
+            const uint32_t lane = c.tid % wl, w = c.tid / wl, nw = c.nthr / wl;
+            const double* __restrict__ colk = M + (uint64_t)k * ld;
+            for (uint32_t j = w; j < m; j += nw) {
+                if (j == k) continue;
+                double* __restrict__ col = M + (uint64_t)j * ld;
+                const double rj = col[k];
+                for (uint32_t i = lane; i < m; i += wl) {
+                    if (i != k) col[i] -= colk[i] * rj;
+                }
             }
         }
         c.sync();
@@ -195,9 +235,27 @@ struct BigDiagKernel {
         double* D = reinterpret_cast<double*>(c.smem);  // nb x nb, ld NB
         uint32_t* lperm = reinterpret_cast<uint32_t*>(D + NB * NB);
         int* sh = reinterpret_cast<int*>(lperm + NB);
-        if (kb == 0) {
-            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) f.rowperm[i] = i;
+#ifndef SANM_HOSTEMU
+        {
+            // 4 warps, warp w owns columns 8w..8w+7 (gj32.cuh)
+            const uint32_t lane = c.tid & 31, j0 = (c.tid >> 5) * 8;
+            double* __restrict__ G = f.F + (uint64_t)kb * f.nr + kb;
+            double v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                v[j] = (lane < nb && j0 + j < nb) ? G[(uint64_t)(j0 + j) * f.nr + lane] : 0.0;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) D[(j0 + j) * NB + lane] = v[j];
+            double* acol = reinterpret_cast<double*>(sh + 2);
+            __syncthreads();
+            block_gj32(D, nb, lperm, acol, amax[0] * 1e-13, nr_perturbed);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (lane < nb && j0 + j < nb) G[(uint64_t)(j0 + j) * f.nr + lane] = D[(j0 + j) * NB + lane];
+            }
         }
+#else
         for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
             uint32_t i = e % nb, j = e / nb;
             D[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
@@ -210,15 +268,14 @@ struct BigDiagKernel {
             uint32_t i = e % nb, j = e / nb;
             f.F[(uint64_t)(kb + j) * f.nr + kb + i] = D[j * NB + i];
         }
+#endif
         // row i of the block now holds original row lperm[i]; the rest of
         // the block row is permuted by BigRowPanelKernel while it loads it
         for (uint32_t i = c.tid; i < nb; i += c.nthr) f.lperm[i] = lperm[i];
         c.sync();
-        if (c.tid == 0) {
-            uint32_t tmp[NB];
-            for (uint32_t i = 0; i < nb; ++i) tmp[i] = f.rowperm[kb + lperm[i]];
-            for (uint32_t i = 0; i < nb; ++i) f.rowperm[kb + i] = tmp[i];
-        }
+        // pivoting never leaves the block: position kb + i of the front holds
+        // the original row kb + lperm[i]
+        for (uint32_t i = c.tid; i < nb; i += c.nthr) f.rowperm[kb + i] = kb + lperm[i];
     }
 };
 
@@ -691,9 +748,10 @@ void SparseLU::factor(const double* vals_dev) {
             const uint32_t* list = I.big_list.ptr() + L.big_off;
             const uint32_t tiles = (L.big_max_nr + 63) / 64;
             for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
+                // 4 warps per front (gj32.cuh)
                 rt::for_each_block(
-                        L.big_n, 256,
-                        NB * NB * sizeof(double) + NB * sizeof(uint32_t) + 16,
+                        L.big_n, 128,
+                        (NB * NB + 2 * NB) * sizeof(double) + NB * sizeof(uint32_t) + 16,
                         BigDiagKernel{I.fd.ptr(), list, kb, amax, npert});
                 rt::for_each_block((size_t)L.big_n * tiles, 256,
                                    (NB * NB + NB * 64) * sizeof(double),
