@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include "cache.h"
 #include "sparse_symbolic.h"
+#include "prof.h"
 #ifndef SANM_HOSTEMU
 #include "gj32.cuh"
 #endif
@@ -15,6 +16,16 @@
 namespace sanm_b200 {
 
 namespace {
+
+//! per-kernel-type device times of the factor / solve phases (SANM_LU_PROF=1;
+//! the event pairs cost ~2 us per launch, so off by default)
+const bool g_lu_prof = getenv("SANM_LU_PROF") != nullptr;
+struct LuScope {
+    std::unique_ptr<prof::Scope> s;
+    explicit LuScope(const char* tag) {
+        if (g_lu_prof) s.reset(new prof::Scope{tag});
+    }
+};
 
 constexpr int NB = 32;          //!< pivot block of the large-front path
 constexpr uint32_t SMALL_NR = 104;  //!< fronts up to this size live in smem
@@ -28,6 +39,7 @@ struct FrontD {
     const int32_t* inv;  //!< map parent row -> own update row (size nr_parent)
     uint32_t* rowperm;   //!< [nc] row permutation of the pivot block
     uint32_t* lperm;     //!< [NB] row permutation of the current pivot step
+    const uint32_t* gptr;  //!< [nr + 1] child contributions of row i: gsrc[gptr[i] .. gptr[i+1])
     uint32_t nr, nc, c0;
     uint32_t child_begin, child_end;
     int32_t parent;
@@ -400,43 +412,84 @@ struct BigColPanelKernel {
 
 /* ---- solves */
 
-/* Solve kernels.  A task is one chunk of SOLVE_ROWS rows of one front; a
- * block of SOLVE_THREADS threads = SOLVE_WARPS groups of 32 lanes.  Lane l owns
- * row l of the chunk (column-major fronts: the 32 lanes read 32 consecutive
- * doubles), group g accumulates columns g, g + SOLVE_WARPS, ... with four
- * independent accumulators, and the groups' partial sums are added in fixed
- * order through shared memory, so results are bitwise reproducible and a
- * dense front of any size spreads over nr/32 blocks x 8 warps. */
-constexpr int SOLVE_ROWS = 32;
-//! column groups per block: 8 for levels of small fronts, 32 where a front has
-//! many columns (the sequential chain of L2-latency-bound loads per lane is
-//! what bounds a level, so wide fronts get more groups)
-constexpr int SOLVE_WARPS_NARROW = 8, SOLVE_WARPS_WIDE = 32;
+/* Solve kernels.  A task is one chunk of ROWS rows of one front; a block of
+ * ROWS x GROUPS threads.  Thread (g, r) owns row r of the chunk and
+ * accumulates columns g, g + GROUPS, ...; the partial sums of the groups are
+ * added in a fixed order through shared memory, so results are bitwise
+ * reproducible.  What bounds a level is memory latency, not bandwidth (the
+ * factors are L2-resident and a level has few fronts): chunks are therefore
+ * only 8 rows (64-byte column segments, still whole sectors) so that a big
+ * front spreads over nr/8 blocks, and every thread keeps 8 independent loads
+ * in flight. */
+//! backward sweep (rows of nr columns): 8-row chunks, 32 column groups for
+//! levels of small fronts, 128 where a front has many columns
+constexpr int BWD_ROWS = 8, BWD_GROUPS_NARROW = 32, BWD_GROUPS_WIDE = 128;
+//! forward sweep (rows of only nc columns, and every chunk first rebuilds the
+//! front's w1 from the children): fewer, larger chunks
+constexpr int FWD_ROWS = 32, FWD_GROUPS_NARROW = 8, FWD_GROUPS_WIDE = 32;
 constexpr uint32_t SOLVE_WIDE_COLS = 192;
+constexpr int SOLVE_STAGE = 8;  //!< partials summed per thread in stage 1
 
-//! partial dot products of rows [r0, r0+32) of a column-major block with v
-template <int SOLVE_WARPS>
-SANM_HD inline double solve_partial(const double* col0, uint64_t ld,
-                                    uint32_t ncol, const double* v, int g) {
-    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    uint32_t j = g;
-    for (; j + 3 * SOLVE_WARPS < ncol; j += 4 * SOLVE_WARPS) {
-        a0 += col0[(uint64_t)j * ld] * v[j];
-        a1 += col0[(uint64_t)(j + SOLVE_WARPS) * ld] * v[j + SOLVE_WARPS];
-        a2 += col0[(uint64_t)(j + 2 * SOLVE_WARPS) * ld] * v[j + 2 * SOLVE_WARPS];
-        a3 += col0[(uint64_t)(j + 3 * SOLVE_WARPS) * ld] * v[j + 3 * SOLVE_WARPS];
+//! partial dot product of one row of a column-major block with v
+template <int GROUPS>
+SANM_HD inline double solve_partial(const double* __restrict__ col0, uint64_t ld,
+                                    uint32_t ncol, const double* __restrict__ v,
+                                    int g) {
+    constexpr int U = 8;
+    double acc[U] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (uint32_t j = g; j < ncol; j += U * GROUPS) {
+        double a[U], x[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t jj = j + u * GROUPS;
+            const bool ok = jj < ncol;
+            a[u] = ok ? col0[(uint64_t)jj * ld] : 0.0;
+            x[u] = ok ? v[jj] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) acc[u] += a[u] * x[u];
     }
-    for (; j < ncol; j += SOLVE_WARPS) a0 += col0[(uint64_t)j * ld] * v[j];
-    return (a0 + a1) + (a2 + a3);
+    return ((acc[0] + acc[1]) + (acc[2] + acc[3])) +
+           ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+}
+
+/*! fixed-order sum of the GROUPS partials of every row: part[g * ROWS + r] ->
+ * returns (for threads with c.tid < ROWS, after two syncs) the row sums in
+ * part[0 .. ROWS) */
+template <int SOLVE_ROWS, int GROUPS>
+SANM_D inline void solve_reduce(const rt::BlockCtx& c, double* part) {
+    constexpr int S1 = GROUPS / SOLVE_STAGE;  // stage-1 threads per row
+    double* st1 = part + SOLVE_ROWS * GROUPS;
+    c.sync();
+    for (int t = c.tid; t < SOLVE_ROWS * S1; t += c.nthr) {
+        const int r = t % SOLVE_ROWS, q = t / SOLVE_ROWS;
+        double s = 0;
+#pragma unroll
+        for (int u = 0; u < SOLVE_STAGE; ++u) s += part[(q * SOLVE_STAGE + u) * SOLVE_ROWS + r];
+        st1[q * SOLVE_ROWS + r] = s;
+    }
+    c.sync();
+    for (int r = c.tid; r < SOLVE_ROWS; r += c.nthr) {
+        double s = 0;
+#pragma unroll
+        for (int q = 0; q < S1; ++q) s += st1[q * SOLVE_ROWS + r];
+        part[r] = s;
+    }
+    // the threads that continue with part[r] are the ones that wrote it
+}
+template <int SOLVE_ROWS, int GROUPS>
+constexpr size_t solve_scratch_doubles() {
+    return (size_t)SOLVE_ROWS * GROUPS + (size_t)SOLVE_ROWS * (GROUPS / SOLVE_STAGE);
 }
 
 //! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates;
 //! b is read through the fill-reducing permutation
-template <int SOLVE_WARPS>
+template <int SOLVE_ROWS, int GROUPS>
 struct ForwardKernel {
-    static constexpr int SOLVE_THREADS = SOLVE_ROWS * SOLVE_WARPS;
+    static constexpr int SOLVE_THREADS = SOLVE_ROWS * GROUPS;
     const FrontD* fronts;
-    const uint32_t* child_list;
+    const uint32_t* gsrc;  // flattened child-update sources (offsets into vecs)
+    const double* vecs;
     const Task* tasks;
     const double* b;       // right-hand side, original numbering
     const uint32_t* perm;  // new index -> original index
@@ -447,12 +500,10 @@ struct ForwardKernel {
         double* w1p = w1 + f.nc;
         double* part = w1p + f.nc;
         for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
+            // child updates in child order (flattened at analysis time: offsets
+            // into the work vectors), so the sum is the one of the tree walk
             double v = b[perm[f.c0 + i]];
-            for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
-                const FrontD ch = fronts[child_list[q]];
-                const int32_t ii = ch.inv[i];
-                if (ii >= 0) v += ch.vec[ch.nc + ii];
-            }
+            for (uint32_t p = f.gptr[i], pe = f.gptr[i + 1]; p < pe; ++p) v += vecs[gsrc[p]];
             w1[i] = v;
         }
         c.sync();
@@ -466,30 +517,27 @@ struct ForwardKernel {
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
             const uint32_t r = r0 + lane;
-            part[th] = r < nu ? solve_partial<SOLVE_WARPS>(f.F + f.nc + r, f.nr, f.nc, w1p, g)
+            part[th] = r < nu ? solve_partial<GROUPS>(f.F + f.nc + r, f.nr, f.nc, w1p, g)
                               : 0.0;
         }
-        c.sync();
+        solve_reduce<SOLVE_ROWS, GROUPS>(c, part);
         for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
             const uint32_t r = r0 + lane;
             if (r >= nu) continue;
             double acc = 0;
-            for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
-                const FrontD ch = fronts[child_list[q]];
-                const int32_t ii = ch.inv[f.nc + r];
-                if (ii >= 0) acc += ch.vec[ch.nc + ii];
+            for (uint32_t p = f.gptr[f.nc + r], pe = f.gptr[f.nc + r + 1]; p < pe; ++p) {
+                acc += vecs[gsrc[p]];
             }
-            for (int g = 0; g < SOLVE_WARPS; ++g) acc += part[g * SOLVE_ROWS + lane];
-            f.vec[f.nc + r] = acc;
+            f.vec[f.nc + r] = acc + part[lane];
         }
     }
 };
 
 //! backward: x1 = G w1' - F12' x2, written to the permuted work vector (read
 //! by descendants) and to the caller's vector in original numbering
-template <int SOLVE_WARPS>
+template <int SOLVE_ROWS, int GROUPS>
 struct BackwardKernel {
-    static constexpr int SOLVE_THREADS = SOLVE_ROWS * SOLVE_WARPS;
+    static constexpr int SOLVE_THREADS = SOLVE_ROWS * GROUPS;
     const FrontD* fronts;
     const Task* tasks;
     double* xp;  // permuted solution
@@ -507,14 +555,13 @@ struct BackwardKernel {
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
             const uint32_t r = r0 + lane;
-            part[th] = r < f.nc ? solve_partial<SOLVE_WARPS>(f.F + r, f.nr, f.nr, v, g) : 0.0;
+            part[th] = r < f.nc ? solve_partial<GROUPS>(f.F + r, f.nr, f.nr, v, g) : 0.0;
         }
-        c.sync();
+        solve_reduce<SOLVE_ROWS, GROUPS>(c, part);
         for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
             const uint32_t r = r0 + lane;
             if (r >= f.nc) continue;
-            double acc = 0;
-            for (int g = 0; g < SOLVE_WARPS; ++g) acc += part[g * SOLVE_ROWS + lane];
+            const double acc = part[lane];
             xp[f.c0 + r] = acc;
             x[perm[f.c0 + r]] = acc;
         }
@@ -540,6 +587,7 @@ struct SparseLU::Impl {
     std::shared_ptr<const Symbolic> sym;
     std::vector<uint32_t> h_rowptr, h_colidx;
     rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list, rowperm, lperm;
+    rt::DBuf<uint32_t> gptr, gsrc;
     rt::DBuf<int32_t> inv;
     rt::DBuf<uint64_t> a_dest;
     rt::DBuf<double> fronts, vecs, vals, bp, xp, scal;
@@ -609,6 +657,30 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.counters.alloc(4);
     I.counters.zero();
 
+    // flattened gather lists of the forward sweep: for row i of front s the
+    // positions (in the work-vector array) of the children's update entries
+    // that land on it, in child order
+    {
+        std::vector<uint32_t> gptr(S.soff[S.nsn] + S.nsn + 1), gsrc;
+        size_t at = 0;
+        for (uint32_t s = 0; s < S.nsn; ++s) {
+            const uint32_t nr = S.sn_nr[s];
+            for (uint32_t i = 0; i < nr; ++i) {
+                gptr[at++] = (uint32_t)gsrc.size();
+                for (uint32_t q = S.child_ptr[s]; q < S.child_ptr[s + 1]; ++q) {
+                    const uint32_t ch = S.child_list[q];
+                    const int32_t ii = S.inv[S.inv_off[ch] + i];
+                    if (ii >= 0) gsrc.push_back((uint32_t)(S.soff[ch] + S.sn_nc[ch] + ii));
+                }
+            }
+            gptr[at++] = (uint32_t)gsrc.size();
+        }
+        sanm_check(gsrc.size() < (1ull << 32) && S.soff[S.nsn] < (1ull << 32));
+        if (gsrc.empty()) gsrc.push_back(0);
+        I.gptr.upload(gptr);
+        I.gsrc.upload(gsrc);
+    }
+
     std::vector<FrontD> fd(S.nsn);
     uint32_t max_front = 0;
     for (uint32_t s = 0; s < S.nsn; ++s) {
@@ -619,6 +691,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         f.inv = S.sn_parent[s] >= 0 ? I.inv.ptr() + S.inv_off[s] : nullptr;
         f.rowperm = I.rowperm.ptr() + S.sn_c0[s];
         f.lperm = I.lperm.ptr() + (size_t)s * NB;
+        f.gptr = I.gptr.ptr() + S.soff[s] + s;
         f.nr = S.sn_nr[s];
         f.nc = S.sn_nc[s];
         f.c0 = S.sn_c0[s];
@@ -660,9 +733,9 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                 L.big_max_nc = std::max(L.big_max_nc, nc);
                 L.big_max_nr = std::max(L.big_max_nr, nr);
             }
-            uint32_t nf = std::max<uint32_t>(1, (nu + SOLVE_ROWS - 1) / SOLVE_ROWS);
+            uint32_t nf = std::max<uint32_t>(1, (nu + FWD_ROWS - 1) / FWD_ROWS);
             for (uint32_t t = 0; t < nf; ++t) fwd_t.push_back({s, t});
-            uint32_t nbk = (nc + SOLVE_ROWS - 1) / SOLVE_ROWS;
+            uint32_t nbk = (nc + BWD_ROWS - 1) / BWD_ROWS;
             for (uint32_t t = 0; t < nbk; ++t) bwd_t.push_back({s, t});
             L.max_nc = std::max(L.max_nc, nc);
             L.max_nr = std::max(L.max_nr, nr);
@@ -733,12 +806,14 @@ void SparseLU::factor(const double* vals_dev) {
     int* npert = I.counters.ptr();
     for (auto& L : I.levels) {
         if (L.asm_n) {
+            LuScope ps{"lu_asm"};
             rt::for_each_block(L.asm_n, 256, 0,
                                AssembleChildren{I.fd.ptr(), I.child_list.ptr(),
                                                 I.asm_tasks.ptr() + L.asm_off});
         }
         if (L.small_n) {
             size_t smem = (size_t)L.small_max_nr * L.small_max_nr * sizeof(double) + 16;
+            LuScope ps{"lu_small"};
             rt::for_each_block(L.small_n, 256, smem,
                                SmallFrontKernel{I.fd.ptr(),
                                                 I.small_list.ptr() + L.small_off,
@@ -748,20 +823,32 @@ void SparseLU::factor(const double* vals_dev) {
             const uint32_t* list = I.big_list.ptr() + L.big_off;
             const uint32_t tiles = (L.big_max_nr + 63) / 64;
             for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
-                // 4 warps per front (gj32.cuh)
-                rt::for_each_block(
-                        L.big_n, 128,
-                        (NB * NB + 2 * NB) * sizeof(double) + NB * sizeof(uint32_t) + 16,
-                        BigDiagKernel{I.fd.ptr(), list, kb, amax, npert});
-                rt::for_each_block((size_t)L.big_n * tiles, 256,
-                                   (NB * NB + NB * 64) * sizeof(double),
-                                   BigRowPanelKernel{I.fd.ptr(), list, kb, tiles});
-                rt::for_each_block((size_t)L.big_n * tiles * tiles, 256,
-                                   2 * NB * 64 * sizeof(double),
-                                   BigGemmKernel{I.fd.ptr(), list, kb, tiles});
-                rt::for_each_block((size_t)L.big_n * tiles, 256,
-                                   (NB * NB + NB * 64) * sizeof(double),
-                                   BigColPanelKernel{I.fd.ptr(), list, kb, tiles});
+                {
+                    LuScope ps{"lu_diag"};
+                    // 4 warps per front (gj32.cuh)
+                    rt::for_each_block(
+                            L.big_n, 128,
+                            (NB * NB + 2 * NB) * sizeof(double) + NB * sizeof(uint32_t) + 16,
+                            BigDiagKernel{I.fd.ptr(), list, kb, amax, npert});
+                }
+                {
+                    LuScope ps{"lu_row"};
+                    rt::for_each_block((size_t)L.big_n * tiles, 256,
+                                       (NB * NB + NB * 64) * sizeof(double),
+                                       BigRowPanelKernel{I.fd.ptr(), list, kb, tiles});
+                }
+                {
+                    LuScope ps{"lu_gemm"};
+                    rt::for_each_block((size_t)L.big_n * tiles * tiles, 256,
+                                       2 * NB * 64 * sizeof(double),
+                                       BigGemmKernel{I.fd.ptr(), list, kb, tiles});
+                }
+                {
+                    LuScope ps{"lu_col"};
+                    rt::for_each_block((size_t)L.big_n * tiles, 256,
+                                       (NB * NB + NB * 64) * sizeof(double),
+                                       BigColPanelKernel{I.fd.ptr(), list, kb, tiles});
+                }
             }
         }
     }
@@ -773,40 +860,47 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
     sanm_check(I.factored, "solve() before factor()");
     // b may alias x: the forward sweep has consumed b before the backward
     // sweep writes x
+    char tag[32];
     for (auto& L : I.levels) {
+        snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - I.levels.data()));
+        LuScope ps{tag};
+        constexpr int R = FWD_ROWS;
         if (L.max_nc >= SOLVE_WIDE_COLS) {
-            constexpr int W = SOLVE_WARPS_WIDE;
+            constexpr int G = FWD_GROUPS_WIDE;
             rt::for_each_block(
-                    L.fwd_n, SOLVE_ROWS * W,
-                    (2 * (size_t)L.max_nc + SOLVE_ROWS * W) * sizeof(double),
-                    ForwardKernel<W>{I.fd.ptr(), I.child_list.ptr(),
+                    L.fwd_n, R * G,
+                    (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
+                    ForwardKernel<R, G>{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
                                      I.fwd_tasks.ptr() + L.fwd_off, b_dev,
                                      I.perm.ptr()});
         } else {
-            constexpr int W = SOLVE_WARPS_NARROW;
+            constexpr int G = FWD_GROUPS_NARROW;
             rt::for_each_block(
-                    L.fwd_n, SOLVE_ROWS * W,
-                    (2 * (size_t)L.max_nc + SOLVE_ROWS * W) * sizeof(double),
-                    ForwardKernel<W>{I.fd.ptr(), I.child_list.ptr(),
+                    L.fwd_n, R * G,
+                    (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
+                    ForwardKernel<R, G>{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
                                      I.fwd_tasks.ptr() + L.fwd_off, b_dev,
                                      I.perm.ptr()});
         }
     }
     for (size_t l = I.levels.size(); l-- > 0;) {
         auto& L = I.levels[l];
+        snprintf(tag, sizeof(tag), "lu_bwd_%02d", (int)l);
+        LuScope ps{tag};
+        constexpr int R = BWD_ROWS;
         if (L.max_nr >= SOLVE_WIDE_COLS) {
-            constexpr int W = SOLVE_WARPS_WIDE;
+            constexpr int G = BWD_GROUPS_WIDE;
             rt::for_each_block(
-                    L.bwd_n, SOLVE_ROWS * W,
-                    ((size_t)L.max_nr + SOLVE_ROWS * W) * sizeof(double),
-                    BackwardKernel<W>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
+                    L.bwd_n, R * G,
+                    ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
+                    BackwardKernel<R, G>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
                                       I.xp.ptr(), x_dev, I.perm.ptr()});
         } else {
-            constexpr int W = SOLVE_WARPS_NARROW;
+            constexpr int G = BWD_GROUPS_NARROW;
             rt::for_each_block(
-                    L.bwd_n, SOLVE_ROWS * W,
-                    ((size_t)L.max_nr + SOLVE_ROWS * W) * sizeof(double),
-                    BackwardKernel<W>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
+                    L.bwd_n, R * G,
+                    ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
+                    BackwardKernel<R, G>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
                                       I.xp.ptr(), x_dev, I.perm.ptr()});
         }
     }
