@@ -177,6 +177,66 @@ class NestedDissection {
 
     u32 stamp = 1;  //!< levels are stored as stamp + l so scratch needs no reset
 
+    std::vector<int32_t> key;  //!< scratch: bisection key of each node
+    struct Cut {
+        bool valid = false, sep_from_left = true;
+        int32_t c = 0;
+        u64 sepw = 0;
+    };
+
+    /*! best threshold of key[] over the nodes of region r: minimum separator
+     * weight among the thresholds that leave both sides >= 30 % (then 20 %) of
+     * the weight.  O(edges). */
+    Cut best_cut(const std::vector<u32>& nodes, u32 r, u64 wt) {
+        int32_t kmin = INT32_MAX, kmax = INT32_MIN;
+        for (u32 v : nodes) {
+            kmin = std::min(kmin, key[v]);
+            kmax = std::max(kmax, key[v]);
+        }
+        Cut best;
+        if (kmax - kmin < 2) return best;
+        const size_t nb = (size_t)(kmax - kmin) + 2;
+        std::vector<int64_t> wk(nb, 0), dl(nb, 0), dr(nb, 0);
+        for (u32 v : nodes) {
+            int32_t kv = key[v], mx = kv, mn = kv;
+            for (auto p = g.begin(v); p != g.end(v); ++p) {
+                if (region[*p] != r) continue;
+                mx = std::max(mx, key[*p]);
+                mn = std::min(mn, key[*p]);
+            }
+            wk[kv - kmin] += w[v];
+            if (mx > kv) {  // v is on the left boundary for c in [kv, mx - 1]
+                dl[kv - kmin] += w[v];
+                dl[mx - kmin] -= w[v];
+            }
+            if (mn < kv) {  // v is on the right boundary for c in [mn, kv - 1]
+                dr[mn - kmin] += w[v];
+                dr[kv - kmin] -= w[v];
+            }
+        }
+        for (int pass = 0; pass < 2 && !best.valid; ++pass) {
+            const u64 share = pass == 0 ? 3 : 2;
+            int64_t wl = 0, bl = 0, br = 0;
+            for (int32_t c = kmin; c < kmax; ++c) {
+                wl += wk[c - kmin];
+                bl += dl[c - kmin];
+                br += dr[c - kmin];
+                const bool from_left = bl <= br;
+                const u64 sw = (u64)(from_left ? bl : br);
+                const u64 lw = (u64)(from_left ? wl - bl : wl);
+                const u64 rw = (u64)(from_left ? (int64_t)wt - wl : (int64_t)wt - wl - br);
+                if (std::min(lw, rw) * 10 < wt * share) continue;
+                if (!best.valid || sw < best.sepw) {
+                    best.valid = true;
+                    best.sepw = sw;
+                    best.c = c;
+                    best.sep_from_left = from_left;
+                }
+            }
+        }
+        return best;
+    }
+
     void dissect(std::vector<u32> nodes) {
         while (true) {
             if (nodes.empty()) return;
@@ -219,44 +279,85 @@ class NestedDissection {
                 emit_leaf(nodes, r);
                 return;
             }
-            // weight per level; pick the lightest level in the middle band
-            std::vector<u64> lw(nlev, 0);
-            for (u32 v : queue) lw[level[v] - base] += w[v];
-            u64 acc = 0;
-            u32 best = nlev / 2;
-            u64 best_w = ~0ull;
-            for (u32 l = 0; l < nlev; ++l) {
-                u64 before = acc;
-                acc += lw[l];
-                u64 after = wt - acc;
-                if (l == 0 || l + 1 == nlev) continue;
-                // both sides must keep a reasonable share
-                u64 mn = std::min(before, after);
-                if (mn * 10 < wt * 3) continue;
-                if (lw[l] < best_w) {
-                    best_w = lw[l];
-                    best = l;
+            // Candidate bisections: thresholds of a node key.  Key 1 is the BFS
+            // level from the pseudo-peripheral root s (spherical shells); key 2
+            // is d_s - d_t with t the node farthest from s, whose level sets are
+            // the much flatter "perpendicular bisectors" of the body.  For a
+            // threshold c the sides are {key <= c} and {key > c}; the vertex
+            // separator is the lighter of the two boundaries.
+            const u32 t_far = queue.back();
+            std::vector<u32> nodes_bfs(queue.begin(), queue.end());
+            for (u32 v : nodes_bfs) key[v] = (int32_t)(level[v] - base);
+            Cut cut1 = best_cut(nodes_bfs, r, wt);
+            std::vector<int32_t> key1;
+            if (nodes_bfs.size() > 64) {
+                key1.reserve(nodes_bfs.size());
+                for (u32 v : nodes_bfs) key1.push_back(key[v]);
+                u32 base2 = new_stamp(nodes.size());
+                bfs(t_far, r, base2);
+                for (size_t q = 0; q < nodes_bfs.size(); ++q) {
+                    u32 v = nodes_bfs[q];
+                    key[v] = key1[q] - (int32_t)(level[v] - base2);
                 }
+                Cut cut2 = best_cut(nodes_bfs, r, wt);
+                std::vector<int32_t> keep;  // key of the best cut so far
+                auto take = [&](const Cut& cnew) {
+                    if (cnew.valid && (!cut1.valid || cnew.sepw < cut1.sepw)) {
+                        cut1 = cnew;
+                        keep.resize(nodes_bfs.size());
+                        for (size_t q = 0; q < nodes_bfs.size(); ++q) keep[q] = key[nodes_bfs[q]];
+                    }
+                };
+                keep = key1;
+                take(cut2);
+                // a second axis: u = the node farthest off the s-t axis (largest
+                // d_s + d_t), u' = the node farthest from u
+                if (nodes_bfs.size() > 512) {
+                    u32 u_off = nodes_bfs[0];
+                    int64_t best_sum = -1;
+                    for (size_t q = 0; q < nodes_bfs.size(); ++q) {
+                        u32 v = nodes_bfs[q];
+                        int64_t sum = (int64_t)key1[q] + (int64_t)(level[v] - base2);
+                        if (sum > best_sum) {
+                            best_sum = sum;
+                            u_off = v;
+                        }
+                    }
+                    u32 base3 = new_stamp(nodes.size());
+                    bfs(u_off, r, base3);
+                    const u32 u_far = queue.back();
+                    std::vector<int32_t> du(nodes_bfs.size());
+                    for (size_t q = 0; q < nodes_bfs.size(); ++q) {
+                        du[q] = (int32_t)(level[nodes_bfs[q]] - base3);
+                    }
+                    u32 base4 = new_stamp(nodes.size());
+                    bfs(u_far, r, base4);
+                    for (size_t q = 0; q < nodes_bfs.size(); ++q) {
+                        u32 v = nodes_bfs[q];
+                        key[v] = du[q] - (int32_t)(level[v] - base4);
+                    }
+                    take(best_cut(nodes_bfs, r, wt));
+                }
+                for (size_t q = 0; q < nodes_bfs.size(); ++q) key[nodes_bfs[q]] = keep[q];
             }
-            // separator = nodes of level `best` that touch level best+1
+            if (!cut1.valid) {
+                emit_leaf(nodes, r);
+                return;
+            }
             std::vector<u32> left, right, sep;
             u32 rl = next_region++, rr = next_region++, rs = next_region++;
-            for (u32 v : queue) {
-                u32 l = level[v] - base;
-                if (l < best) {
-                    left.push_back(v);
-                } else if (l > best) {
-                    right.push_back(v);
-                } else {
-                    bool touch = false;
+            for (u32 v : nodes_bfs) {
+                const bool in_left = key[v] <= cut1.c;
+                bool touch = false;
+                if (in_left == cut1.sep_from_left) {
                     for (auto p = g.begin(v); p != g.end(v); ++p) {
-                        if (region[*p] == r && level[*p] == base + best + 1) {
+                        if (region[*p] == r && (key[*p] <= cut1.c) != in_left) {
                             touch = true;
                             break;
                         }
                     }
-                    (touch ? sep : left).push_back(v);
                 }
+                (touch ? sep : in_left ? left : right).push_back(v);
             }
             for (u32 v : left) region[v] = rl;
             for (u32 v : right) region[v] = rr;
@@ -313,6 +414,7 @@ public:
         region.assign(n, 1);
         next_region = 2;
         level.assign(n, 0);
+        key.assign(n, 0);
         order.clear();
         order.reserve(n);
         std::vector<u32> all(n);
