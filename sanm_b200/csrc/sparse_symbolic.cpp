@@ -11,7 +11,29 @@
 #include "rt.h"
 
 #include <algorithm>
+#include <atomic>
 #include <numeric>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+namespace {
+struct StageTimer {
+    bool on = getenv("SANM_LU_DEBUG") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    const char* cur = "start";
+    void next(const char* name) {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        printf("[lu-analyze] %-42s %8.2f ms\n", cur,
+               std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+        cur = name;
+    }
+    ~StageTimer() { next("end"); }
+};
+}  // namespace
+#define SANM_STAGE(name) stage_timer.next(name)
 
 namespace sanm_b200 {
 
@@ -53,13 +75,19 @@ Adj build_sym_adj(u32 n, const u32* rowptr, const u32* colidx) {
     }
     Adj a;
     a.ptr.assign(n + 1, 0);
-    a.idx.reserve(raw.size() / 2 + n);
-    for (u32 i = 0; i < n; ++i) {
+    std::vector<u32> ulen(n);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < (int64_t)n; ++i) {
         auto b = raw.begin() + cnt[i], e = raw.begin() + cnt[i + 1];
         std::sort(b, e);
-        e = std::unique(b, e);
-        a.idx.insert(a.idx.end(), b, e);
-        a.ptr[i + 1] = a.idx.size();
+        ulen[i] = (u32)(std::unique(b, e) - b);
+    }
+    for (u32 i = 0; i < n; ++i) a.ptr[i + 1] = a.ptr[i] + ulen[i];
+    a.idx.resize(a.ptr[n]);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < (int64_t)n; ++i) {
+        std::copy(raw.begin() + cnt[i], raw.begin() + cnt[i] + ulen[i],
+                  a.idx.begin() + a.ptr[i]);
     }
     return a;
 }
@@ -150,14 +178,19 @@ class NestedDissection {
     const std::vector<u32>& w;
     std::vector<u32> region;  //!< region id of each node (current partition)
     std::vector<u32> level;   //!< scratch: BFS level
-    std::vector<u32> queue;
     std::vector<u32>& order;
-    u32 next_region = 1;
+    std::atomic<u32> next_region{1};
+    //! per-task state: sub-problems on disjoint node sets run as OpenMP tasks
+    struct Ctx {
+        std::vector<u32> queue, order;
+        u32 stamp = 1;  //!< levels are stored as stamp + l: scratch needs no reset
+    };
     static constexpr u32 LEAF_WEIGHT = 36;
 
     //! BFS inside region r from root; fills queue (visit order) and level;
     //! returns number of levels
-    u32 bfs(u32 root, u32 r, u32 stamp_base) {
+    u32 bfs(Ctx& ctx, u32 root, u32 r, u32 stamp_base) {
+        auto& queue = ctx.queue;
         queue.clear();
         queue.push_back(root);
         level[root] = stamp_base;
@@ -175,9 +208,109 @@ class NestedDissection {
         return nlev;
     }
 
-    u32 stamp = 1;  //!< levels are stored as stamp + l so scratch needs no reset
 
     std::vector<int32_t> key;  //!< scratch: bisection key of each node
+    std::vector<uint8_t> mark;  //!< scratch: 1 = boundary node, 2 = in the cover
+    std::vector<u32> mate, bidx;
+
+    /*! Marks (mark[v] = 2) a minimum vertex cover of the cut edges between
+     * {key <= c} and {key > c} inside region r. */
+    void min_cover_separator(const std::vector<u32>& nodes, u32 r, int32_t c) {
+        std::vector<u32> lb, rb;  // boundary nodes of both sides
+        for (u32 v : nodes) {
+            const bool in_left = key[v] <= c;
+            for (auto p = g.begin(v); p != g.end(v); ++p) {
+                if (region[*p] == r && (key[*p] <= c) != in_left) {
+                    mark[v] = 1;
+                    (in_left ? lb : rb).push_back(v);
+                    break;
+                }
+            }
+        }
+        constexpr u32 NONE = ~0u;
+        for (u32 v : lb) mate[v] = NONE;
+        for (u32 v : rb) mate[v] = NONE;
+        auto cross = [&](u32 v, u32 u) {
+            return region[u] == r && mark[u] && (key[u] <= c) != (key[v] <= c);
+        };
+        // maximum matching by augmenting paths (iterative DFS from each free
+        // left node); the boundaries have at most a few thousand nodes
+        std::vector<u32> stack, visited_r;
+        std::vector<std::pair<u32, const u32*>> st;
+        for (u32 root : lb) {
+            // greedy first
+            for (auto p = g.begin(root); p != g.end(root); ++p) {
+                if (cross(root, *p) && mate[*p] == NONE) {
+                    mate[*p] = root;
+                    mate[root] = *p;
+                    break;
+                }
+            }
+        }
+        for (u32 root : lb) {
+            if (mate[root] != NONE) continue;
+            // DFS over alternating paths; bidx[u] = left predecessor of right u
+            visited_r.clear();
+            st.clear();
+            st.push_back({root, g.begin(root)});
+            u32 found = NONE;
+            while (!st.empty() && found == NONE) {
+                auto& [v, it] = st.back();
+                if (it == g.end(v)) {
+                    st.pop_back();
+                    continue;
+                }
+                u32 u = *it++;
+                if (!cross(v, u) || bidx[u] != NONE) continue;
+                bidx[u] = v;
+                visited_r.push_back(u);
+                if (mate[u] == NONE) {
+                    found = u;
+                } else {
+                    st.push_back({mate[u], g.begin(mate[u])});
+                }
+            }
+            if (found != NONE) {
+                u32 u = found;
+                while (true) {
+                    u32 v = bidx[u], prev = mate[v];
+                    mate[u] = v;
+                    mate[v] = u;
+                    if (v == root) break;
+                    u = prev;
+                }
+            }
+            for (u32 u : visited_r) bidx[u] = NONE;
+        }
+        // Koenig: Z = nodes reachable from free left nodes by alternating
+        // paths; cover = (L \ Z) + (R & Z)
+        std::vector<u32> zl, zr;
+        stack.clear();
+        for (u32 v : lb) {
+            if (mate[v] == NONE) {
+                stack.push_back(v);
+                mark[v] = 3;  // left node in Z
+            }
+        }
+        while (!stack.empty()) {
+            u32 v = stack.back();
+            stack.pop_back();
+            for (auto p = g.begin(v); p != g.end(v); ++p) {
+                u32 u = *p;
+                if (!cross(v, u) || mark[u] == 2) continue;
+                mark[u] = 2;  // right node in Z: in the cover
+                u32 m = mate[u];
+                if (m != NONE && mark[m] != 3) {
+                    mark[m] = 3;
+                    stack.push_back(m);
+                }
+            }
+        }
+        for (u32 v : lb) mark[v] = mark[v] == 3 ? 0 : 2;  // L \ Z is in the cover
+        for (u32 v : rb) {
+            if (mark[v] != 2) mark[v] = 0;
+        }
+    }
     struct Cut {
         bool valid = false, sep_from_left = true;
         int32_t c = 0;
@@ -237,19 +370,21 @@ class NestedDissection {
         return best;
     }
 
-    void dissect(std::vector<u32> nodes) {
+    void dissect(Ctx& ctx, std::vector<u32> nodes) {
+        auto& queue = ctx.queue;
+        auto& order = ctx.order;
         while (true) {
             if (nodes.empty()) return;
             const u32 r = region[nodes[0]];
             u64 wt = 0;
             for (u32 v : nodes) wt += w[v];
             if (wt <= LEAF_WEIGHT || nodes.size() <= 2) {
-                emit_leaf(nodes, r);
+                emit_leaf(ctx, nodes, r);
                 return;
             }
             // connected component of nodes[0]
-            u32 base = new_stamp(nodes.size());
-            bfs(nodes[0], r, base);
+            u32 base = new_stamp(ctx, nodes.size());
+            bfs(ctx, nodes[0], r, base);
             if (queue.size() < nodes.size()) {
                 // disconnected: peel this component off and handle it on its own
                 u32 rc = next_region++;
@@ -260,23 +395,23 @@ class NestedDissection {
                 for (u32 v : nodes) {
                     if (region[v] == r) rest.push_back(v);
                 }
-                dissect(std::move(comp));
+                dissect(ctx, std::move(comp));
                 nodes.swap(rest);
                 continue;
             }
             // pseudo-peripheral root: repeat BFS from the farthest node
             u32 root = queue.back(), nlev = 0;
             for (int it = 0; it < 3; ++it) {
-                base = new_stamp(nodes.size());
-                u32 nl = bfs(root, r, base);
+                base = new_stamp(ctx, nodes.size());
+                u32 nl = bfs(ctx, root, r, base);
                 if (nl <= nlev) break;
                 nlev = nl;
                 root = queue.back();
             }
-            base = new_stamp(nodes.size());
-            nlev = bfs(root, r, base);
+            base = new_stamp(ctx, nodes.size());
+            nlev = bfs(ctx, root, r, base);
             if (nlev < 3) {
-                emit_leaf(nodes, r);
+                emit_leaf(ctx, nodes, r);
                 return;
             }
             // Candidate bisections: thresholds of a node key.  Key 1 is the BFS
@@ -293,8 +428,8 @@ class NestedDissection {
             if (nodes_bfs.size() > 64) {
                 key1.reserve(nodes_bfs.size());
                 for (u32 v : nodes_bfs) key1.push_back(key[v]);
-                u32 base2 = new_stamp(nodes.size());
-                bfs(t_far, r, base2);
+                u32 base2 = new_stamp(ctx, nodes.size());
+                bfs(ctx, t_far, r, base2);
                 for (size_t q = 0; q < nodes_bfs.size(); ++q) {
                     u32 v = nodes_bfs[q];
                     key[v] = key1[q] - (int32_t)(level[v] - base2);
@@ -323,15 +458,15 @@ class NestedDissection {
                             u_off = v;
                         }
                     }
-                    u32 base3 = new_stamp(nodes.size());
-                    bfs(u_off, r, base3);
+                    u32 base3 = new_stamp(ctx, nodes.size());
+                    bfs(ctx, u_off, r, base3);
                     const u32 u_far = queue.back();
                     std::vector<int32_t> du(nodes_bfs.size());
                     for (size_t q = 0; q < nodes_bfs.size(); ++q) {
                         du[q] = (int32_t)(level[nodes_bfs[q]] - base3);
                     }
-                    u32 base4 = new_stamp(nodes.size());
-                    bfs(u_far, r, base4);
+                    u32 base4 = new_stamp(ctx, nodes.size());
+                    bfs(ctx, u_far, r, base4);
                     for (size_t q = 0; q < nodes_bfs.size(); ++q) {
                         u32 v = nodes_bfs[q];
                         key[v] = du[q] - (int32_t)(level[v] - base4);
@@ -341,58 +476,71 @@ class NestedDissection {
                 for (size_t q = 0; q < nodes_bfs.size(); ++q) key[nodes_bfs[q]] = keep[q];
             }
             if (!cut1.valid) {
-                emit_leaf(nodes, r);
+                emit_leaf(ctx, nodes, r);
                 return;
             }
             std::vector<u32> left, right, sep;
             u32 rl = next_region++, rr = next_region++, rs = next_region++;
+            // smallest vertex separator of this edge cut: a minimum vertex cover
+            // of the bipartite graph of cut edges (Koenig: from a maximum
+            // matching); it may take nodes from both boundaries
+            min_cover_separator(nodes_bfs, r, cut1.c);
             for (u32 v : nodes_bfs) {
-                const bool in_left = key[v] <= cut1.c;
-                bool touch = false;
-                if (in_left == cut1.sep_from_left) {
-                    for (auto p = g.begin(v); p != g.end(v); ++p) {
-                        if (region[*p] == r && (key[*p] <= cut1.c) != in_left) {
-                            touch = true;
-                            break;
-                        }
-                    }
+                if (mark[v] == 2) {
+                    sep.push_back(v);
+                } else {
+                    (key[v] <= cut1.c ? left : right).push_back(v);
                 }
-                (touch ? sep : in_left ? left : right).push_back(v);
+                mark[v] = 0;
             }
             for (u32 v : left) region[v] = rl;
             for (u32 v : right) region[v] = rr;
             for (u32 v : sep) region[v] = rs;
             if (left.empty() || right.empty()) {
                 for (u32 v : nodes) region[v] = r;
-                emit_leaf(nodes, r);
+                emit_leaf(ctx, nodes, r);
                 return;
             }
-            dissect(std::move(left));
-            dissect(std::move(right));
+            if (left.size() + right.size() > 4096) {
+                // independent sub-problems (disjoint nodes, own stamps/queues)
+                Ctx cl, cr;
+                cl.stamp = cr.stamp = ctx.stamp;
+#pragma omp task shared(cl, left) default(shared)
+                dissect(cl, std::move(left));
+                dissect(cr, std::move(right));
+#pragma omp taskwait
+                order.insert(order.end(), cl.order.begin(), cl.order.end());
+                order.insert(order.end(), cr.order.begin(), cr.order.end());
+            } else {
+                dissect(ctx, std::move(left));
+                dissect(ctx, std::move(right));
+            }
             // the separator goes last
             for (u32 v : sep) order.push_back(v);
             return;
         }
     }
 
-    u32 new_stamp(size_t span) {
-        u32 s = stamp;
-        stamp += (u32)span + 2;
+    u32 new_stamp(Ctx& ctx, size_t span) {
+        u32 s = ctx.stamp;
+        ctx.stamp += (u32)span + 2;
         return s;
     }
 
     //! leaves: BFS (Cuthill-McKee-like) order, reversed
-    void emit_leaf(const std::vector<u32>& nodes, u32 r) {
+    void emit_leaf(Ctx& ctx, const std::vector<u32>& nodes, u32 r) {
+        auto& queue = ctx.queue;
+        auto& order = ctx.order;
         size_t start = order.size();
         std::vector<u32> rest(nodes);
         while (!rest.empty()) {
-            u32 base = new_stamp(nodes.size());
+            u32 base = new_stamp(ctx, nodes.size());
             // start from a minimum-degree node of what is left
             u32 root = rest[0];
             for (u32 v : rest) {
                 if (g.deg(v) < g.deg(root)) root = v;
             }
-            bfs(root, r, base);
+            bfs(ctx, root, r, base);
             for (u32 v : queue) {
                 order.push_back(v);
                 region[v] = 0;  // done
@@ -415,13 +563,19 @@ public:
         next_region = 2;
         level.assign(n, 0);
         key.assign(n, 0);
-        order.clear();
-        order.reserve(n);
+        mark.assign(n, 0);
+        mate.assign(n, ~0u);
+        bidx.assign(n, ~0u);
         std::vector<u32> all(n);
         std::iota(all.begin(), all.end(), 0u);
         // stamps grow by O(|region|) per BFS: total O(n log n) << 2^32 for the
-        // sizes this solver targets; guard anyway
-        dissect(std::move(all));
+        // sizes this solver targets
+        Ctx root;
+        root.order.reserve(n);
+#pragma omp parallel
+#pragma omp single
+        dissect(root, std::move(all));
+        order = std::move(root.order);
         sanm_check(order.size() == n, "nested dissection lost nodes: %zu vs %u",
                    order.size(), n);
     }
@@ -431,11 +585,13 @@ public:
 
 Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
                           const uint32_t* colidx) {
+    StageTimer stage_timer;
     Symbolic S;
     S.n = n;
     sanm_check(n > 0);
     Adj adj = build_sym_adj(n, rowptr, colidx);
 
+    SANM_STAGE("ordering");
     // ---- ordering
     u32 nsv = 0;
     std::vector<u32> sv = supervariables(adj, nsv);
@@ -456,6 +612,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
     std::vector<u32> iperm(n);
     for (u32 i = 0; i < n; ++i) iperm[perm[i]] = i;
 
+    SANM_STAGE("elimination tree (Liu) on the permuted s");
     // ---- elimination tree (Liu) on the permuted symmetric pattern
     auto etree = [&](const std::vector<u32>& pm, const std::vector<u32>& ipm,
                      std::vector<int32_t>& parent) {
@@ -483,6 +640,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
     std::vector<int32_t> parent;
     etree(perm, iperm, parent);
 
+    SANM_STAGE("postorder (children before parents, subt");
     // ---- postorder (children before parents, subtrees contiguous)
     {
         std::vector<u32> head(n, ~0u), next(n, ~0u);
@@ -518,6 +676,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         etree(perm, iperm, parent);
     }
 
+    SANM_STAGE("column counts of L (off-diagonal) by row");
     // ---- column counts of L (off-diagonal) by row-subtree traversal
     std::vector<u32> cc(n, 0);
     {
@@ -538,6 +697,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         }
     }
 
+    SANM_STAGE("supernodes: fundamental, then relaxed am");
     // ---- supernodes: fundamental, then relaxed amalgamation with the parent
     struct SN {
         u32 c0, nc, nr;
@@ -600,6 +760,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         for (u32 c = 0; c < sns[s].nc; ++c) col2sn[sns[s].c0 + c] = s;
     }
 
+    SANM_STAGE("front structures (exact, by merging chil");
     // ---- front structures (exact, by merging children)
     S.soff.assign(nsn + 1, 0);
     {
@@ -656,6 +817,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         }
     }
 
+    SANM_STAGE("front storage, child -> parent inverse m");
     // ---- front storage, child -> parent inverse maps, levels
     S.foff.assign(nsn + 1, 0);
     for (u32 s = 0; s < nsn; ++s) {
@@ -708,9 +870,13 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         for (u32 s = 0; s < nsn; ++s) S.level_list[pos[lev[s]]++] = s;
     }
 
+    SANM_STAGE("destinations of the original entries");
     // ---- destinations of the original entries
     S.a_dest.resize(rowptr[n]);
-    for (u32 i = 0; i < n; ++i) {
+    int bad_entry = 0;
+#pragma omp parallel for schedule(static) reduction(| : bad_entry)
+    for (int64_t i64 = 0; i64 < (int64_t)n; ++i64) {
+        const u32 i = (u32)i64;
         u32 pi = iperm[i];
         for (u32 p = rowptr[i]; p < rowptr[i + 1]; ++p) {
             u32 pj = iperm[colidx[p]];
@@ -720,13 +886,16 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
             auto local = [&](u32 g) -> u32 {
                 if (g < c0 + nc) return g - c0;
                 const u32* it = std::lower_bound(st + nc, st + nr, g);
-                sanm_check(it != st + nr && *it == g,
-                           "entry outside the frontal structure");
+                if (it == st + nr || *it != g) {
+                    bad_entry = 1;
+                    return 0;
+                }
                 return (u32)(it - st);
             };
             S.a_dest[p] = S.foff[s] + (u64)local(pj) * nr + local(pi);
         }
     }
+    sanm_check(!bad_entry, "entry outside the frontal structure");
     S.perm = std::move(perm);
     S.iperm = std::move(iperm);
     return S;
