@@ -31,5 +31,9 @@ def load() -> Binding:
             raise ImportError(
                 f"{LIB_PATH} is missing: build it with `python -m "
                 "sanm_b200.build` (needs nvcc); sanm_b200 has no CPU fallback")
+        # load every kernel image when the library is first used instead of at
+        # each kernel's first launch: a solve then never pays module loading
+        # (has to be set before the CUDA context exists to take effect)
+        os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
         _binding = Binding(ctypes.CDLL(LIB_PATH), "sanm_")
     return _binding

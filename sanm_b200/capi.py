@@ -505,7 +505,21 @@ class _ANMBase:
         self.b.call("anm_element_stats", self.h, *[C.byref(v) for v in vals])
         keys = ["tet_order_steps", "element_ms", "solve_ms", "factor_ms",
                 "assemble_ms"]
-        return {k: v.value for k, v in zip(keys, vals)}
+        out = {k: v.value for k, v in zip(keys, vals)}
+        if self.b.has("anm_lu_stats"):
+            u = [_u64() for _ in range(3)]
+            fl = C.c_double()
+            w = [_u64() for _ in range(3)]
+            self.b.call("anm_lu_stats", self.h, C.byref(u[0]), C.byref(u[1]),
+                        C.byref(u[2]), C.byref(fl), C.byref(w[0]),
+                        C.byref(w[1]), C.byref(w[2]))
+            out.update(n=u[0].value, nnz_a=u[1].value,
+                       factor_entries=u[2].value, factor_flops=fl.value,
+                       nr_supernodes=w[0].value, nr_levels=w[1].value,
+                       max_front=w[2].value)
+            out["nr_solves"] = self.b.prof_get("sparse_solve")[1]
+            out["nr_factor"] = self.b.prof_get("sparse_prep")[1]
+        return out
 
 
 class ANMSolverVecScale(_ANMBase):

@@ -275,7 +275,7 @@ KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
     // structural pattern (independent of values): for every output row the
     // union, over the items it touches, of the unknowns those items read
     std::vector<std::vector<uint32_t>> rows(n);
-#pragma omp parallel
+#pragma omp parallel num_threads(::sanm_b200::rt::host_threads())
     {
         std::vector<uint32_t> items, cand;
 #pragma omp for schedule(dynamic, 256)

@@ -62,7 +62,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
         const auto& cf = rin.h_coeff();
         int wu = 0;
         bool bad = false, general = false;
-#pragma omp parallel for reduction(max : wu) reduction(|| : bad, general)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) reduction(max : wu) reduction(|| : bad, general)
         for (int64_t r = 0; r < (int64_t)(N * 9); ++r) {
             int nu = 0, ng = 0;
             bool seen_general = false;
@@ -91,7 +91,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
             gidx.assign((size_t)9 * npad, NONE32);
             gcoef.assign((size_t)9 * npad, 0.0);
         }
-#pragma omp parallel for
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads())
         for (int64_t e = 0; e < (int64_t)N; ++e) {
             for (int q = 0; q < 9; ++q) {
                 const uint64_t r = (uint64_t)e * 9 + q;
@@ -149,7 +149,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
     std::vector<double> nrm((size_t)12 * npad, 0.0);
     std::vector<uint32_t> grow((size_t)12 * npad, NONE32);  // global row of (d, c)
     bool bad = false;
-#pragma omp parallel for reduction(|| : bad)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) reduction(|| : bad)
     for (int64_t e = 0; e < (int64_t)N; ++e) {
         struct RowInfo {
             uint32_t row;
@@ -214,7 +214,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
     // per block: distinct rows -> local ids, contributor lists
     std::vector<uint32_t> blk_cnt(ntiles + 1, 0);
     std::vector<std::vector<uint32_t>> blk_rows(ntiles);
-#pragma omp parallel for
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads())
     for (int64_t b = 0; b < (int64_t)ntiles; ++b) {
         auto& v = blk_rows[b];
         for (int s = 0; s < 12; ++s) {
@@ -233,7 +233,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
     std::vector<uint16_t> lrow((size_t)12 * npad, NONE16);
     std::vector<uint32_t> con_ptr(R + 1, 0);
     std::vector<uint32_t> part_row(R);
-#pragma omp parallel for
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads())
     for (int64_t b = 0; b < (int64_t)ntiles; ++b) {
         const auto& v = blk_rows[b];
         const uint32_t base = blk_cnt[b];
@@ -251,7 +251,7 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
     }
     for (uint64_t g = 0; g < R; ++g) con_ptr[g + 1] += con_ptr[g];
     std::vector<uint16_t> con_idx(con_ptr[R]);
-#pragma omp parallel for
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads())
     for (int64_t b = 0; b < (int64_t)ntiles; ++b) {
         const uint32_t base = blk_cnt[b];
         const uint32_t nloc = blk_cnt[b + 1] - base;

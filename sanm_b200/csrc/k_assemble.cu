@@ -101,7 +101,7 @@ std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
     std::vector<uint8_t> tab((size_t)27 * npad, 0);
     std::vector<uint32_t> dloc((size_t)KE_ENTRIES * N, NONE32);
     bool bad = false;
-#pragma omp parallel for reduction(|| : bad)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) reduction(|| : bad)
     for (int64_t e = 0; e < (int64_t)N; ++e) {
         uint32_t cols[KE_COLS];
         int nc = 0;

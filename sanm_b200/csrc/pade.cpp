@@ -21,7 +21,7 @@ double dot(const double* a, const double* b, size_t n) {
         return s;
     }
     std::vector<double> part(nchunk);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
     for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
         const size_t i0 = c * CHUNK, i1 = std::min(n, i0 + CHUNK);
         double s = 0;
@@ -58,7 +58,7 @@ PadeApproximation::PadeApproximation(std::vector<const double*> xs, size_t len,
             } else {
                 const double f = -a(i, j);
                 const double* o = orth[j].data();
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
                 for (int64_t q = 0; q < (int64_t)len; ++q) u[q] += o[q] * f;
             }
         }
@@ -115,7 +115,7 @@ std::vector<double> PadeApproximation::eval_nume(double a, const double* d,
     for (int i = n; i >= 1; --i) {
         double scale = poly::eval(d, n - i + 1, a);
         const double* x = m_xs[i];
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
         for (int64_t q = 0; q < (int64_t)m_len; ++q) {
             sum[q] = sum[q] * a + x[q] * scale;
         }
@@ -150,7 +150,7 @@ bool PadeApproximation::estimate_valid_range(double start, double eps,
         const double f = denom_n / denom_lo;
         // same fixed chunking as dot()
         std::vector<double> dv(m_len);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
         for (int64_t q = 0; q < (int64_t)m_len; ++q) dv[q] = pl[q] * f - pn[q];
         const double diff2 = dot(dv.data(), dv.data(), m_len),
                      pn2 = dot(pn.data(), pn.data(), m_len);

@@ -1,10 +1,25 @@
 /* sanm_b200/csrc/rt.cu -- runtime layer implementation (see rt.h). */
 #include "rt.h"
 
+#include <omp.h>
+#include <cstdlib>
+
 #include <atomic>
 
 namespace sanm_b200 {
 namespace rt {
+
+int host_threads() {
+    static const int n = [] {
+        if (const char* e = getenv("SANM_HOST_THREADS")) {
+            int v = atoi(e);
+            if (v > 0) return v;
+        }
+        int p = omp_get_num_procs();
+        return p < 1 ? 1 : p > 16 ? 16 : p;
+    }();
+    return n;
+}
 
 namespace {
 std::atomic<uint64_t> g_launches{0};

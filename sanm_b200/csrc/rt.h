@@ -149,6 +149,11 @@ void pipe_sync(int pipe);              //!< host waits for the pipe
 void* hmalloc_pinned(size_t bytes);
 void hfree_pinned(void* p);
 
+//! threads of the host-side parallel loops (analysis, list building, Pade):
+//! SANM_HOST_THREADS or min(cores, 16); independent of omp_set_num_threads()
+//! calls made by other libraries in the process
+int host_threads();
+
 //! number of kernels launched by this library since process start
 uint64_t launch_count();
 void count_launch();

@@ -76,7 +76,7 @@ Adj build_sym_adj(u32 n, const u32* rowptr, const u32* colidx) {
     Adj a;
     a.ptr.assign(n + 1, 0);
     std::vector<u32> ulen(n);
-#pragma omp parallel for schedule(dynamic, 256)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(dynamic, 256)
     for (int64_t i = 0; i < (int64_t)n; ++i) {
         auto b = raw.begin() + cnt[i], e = raw.begin() + cnt[i + 1];
         std::sort(b, e);
@@ -84,7 +84,7 @@ Adj build_sym_adj(u32 n, const u32* rowptr, const u32* colidx) {
     }
     for (u32 i = 0; i < n; ++i) a.ptr[i + 1] = a.ptr[i] + ulen[i];
     a.idx.resize(a.ptr[n]);
-#pragma omp parallel for schedule(static)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
     for (int64_t i = 0; i < (int64_t)n; ++i) {
         std::copy(raw.begin() + cnt[i], raw.begin() + cnt[i] + ulen[i],
                   a.idx.begin() + a.ptr[i]);
@@ -572,7 +572,7 @@ public:
         // sizes this solver targets
         Ctx root;
         root.order.reserve(n);
-#pragma omp parallel
+#pragma omp parallel num_threads(::sanm_b200::rt::host_threads())
 #pragma omp single
         dissect(root, std::move(all));
         order = std::move(root.order);
@@ -874,7 +874,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
     // ---- destinations of the original entries
     S.a_dest.resize(rowptr[n]);
     int bad_entry = 0;
-#pragma omp parallel for schedule(static) reduction(| : bad_entry)
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) reduction(| : bad_entry)
     for (int64_t i64 = 0; i64 < (int64_t)n; ++i64) {
         const u32 i = (u32)i64;
         u32 pi = iperm[i];
