@@ -183,6 +183,18 @@ int sanm_sweep_run(sanm_sweep_t* s);
  * soon as order k has been assembled (two copy streams beside the compute
  * stream); returns when b has arrived.  Same results as the three calls. */
 int sanm_sweep_run_host(sanm_sweep_t* s, const double* x, double* b);
+/* Multi-rank exchange of the assembled right-hand sides.  mode 0 (default):
+ * all-reduce of the full vectors, every rank ends with all of b (what the
+ * replicated solver of the ANM drivers needs).  mode 1: nodal vectors stay
+ * distributed: only the interface rows shared with neighbouring ranks are
+ * exchanged and summed (ncclSend/ncclRecv), rows outside this rank's range are
+ * not touched, and sanm_sweep_run_host() moves only the local ranges of x and
+ * b.  Collective: call it on every rank.  (The reference gathers its worker
+ * shards by memcpy inside one process, libsanm/symbolic.cpp:418-439.) */
+int sanm_sweep_set_exchange(sanm_sweep_t* s, int mode);
+/* ranges4 = {x_lo, x_hi, b_lo, b_hi}: nodal index ranges the local tets read
+ * and contribute to */
+int sanm_sweep_local_ranges(sanm_sweep_t* s, uint64_t* ranges4);
 /* b: host [(order+1), n_out] (rows b_0..b_K); synchronises */
 int sanm_sweep_get_b(sanm_sweep_t* s, double* b);
 /* tet*order steps of one sweep, algorithmic HBM bytes of one sweep (SURVEY 8d:

@@ -630,6 +630,15 @@ class ElementSweep:
         self.b.call("sweep_get_b", self.h, _ptr(out))
         return out
 
+    def set_exchange(self, mode: int):
+        """0: all-reduce of full vectors; 1: distributed vectors, halo sums"""
+        self.b.call("sweep_set_exchange", self.h, C.c_int(mode))
+
+    def local_ranges(self):
+        r = (C.c_uint64 * 4)()
+        self.b.call("sweep_local_ranges", self.h, r)
+        return tuple(int(v) for v in r)
+
     def run_host(self, x, out=None) -> np.ndarray:
         """set_x + run + get_b with the copies overlapped (host buffers)"""
         x = _f64(x)

@@ -3,6 +3,8 @@
 #include "capi_util.h"
 #include "prof.h"
 
+#include <algorithm>
+
 #ifdef SANM_WITH_NCCL
 #include <nccl.h>
 #endif
@@ -50,6 +52,75 @@ void allreduce_sum(double* dev, size_t n) {
     g_cb(g_stage.data(), n);
     rt::h2d(dev, g_stage.data(), n * sizeof(double));
 #endif
+}
+
+namespace {
+struct HaloAdd {
+    double* v;
+    const double* recv;
+    bool recv_first;
+    SANM_D void operator()(size_t i) const {
+        v[i] = recv_first ? recv[i] + v[i] : v[i] + recv[i];
+    }
+};
+}  // namespace
+
+void halo_setup(Halo& h, uint64_t lo, uint64_t hi, uint64_t n) {
+    h.lo = lo;
+    h.hi = hi;
+    h.n = n;
+    h.peers.clear();
+    h.ready = true;
+    if (g_world == 1) return;
+#ifdef SANM_WITH_NCCL
+    if (g_nccl) {
+        std::vector<uint64_t> mine{lo, hi}, all((size_t)2 * g_world);
+        rt::DBuf<uint64_t> dm, da;
+        dm.upload(mine);
+        da.alloc(all.size());
+        SANM_NCCL_CHECK(ncclAllGather(dm.ptr(), da.ptr(), 2, ncclUint64, g_nccl,
+                                      rt::stream()));
+        da.download(all.data(), all.size());
+        size_t off = 0;
+        for (int q = 0; q < g_world; ++q) {
+            if (q == g_rank) continue;
+            const uint64_t olo = std::max(lo, all[2 * q]);
+            const uint64_t ohi = std::min(hi, all[2 * q + 1]);
+            if (olo >= ohi) continue;
+            h.peers.push_back({q, olo, ohi - olo, off});
+            off += ohi - olo;
+        }
+        h.scratch.alloc(off ? off : 1);
+    }
+#endif
+}
+
+void halo_sum(double* dev, Halo& h) {
+    sanm_check(h.ready, "halo_sum() before halo_setup()");
+    if (g_world == 1) return;
+    SANM_PROF("comm_halo");
+#ifdef SANM_WITH_NCCL
+    if (g_nccl) {
+        if (h.peers.empty()) return;
+        rt::count_launch();
+        SANM_NCCL_CHECK(ncclGroupStart());
+        for (auto& p : h.peers) {
+            SANM_NCCL_CHECK(ncclSend(dev + p.lo, p.cnt, ncclDouble, p.rank, g_nccl,
+                                     rt::stream()));
+            SANM_NCCL_CHECK(ncclRecv(h.scratch.ptr() + p.scratch_off, p.cnt,
+                                     ncclDouble, p.rank, g_nccl, rt::stream()));
+        }
+        SANM_NCCL_CHECK(ncclGroupEnd());
+        // peers are in ascending rank order: lower ranks' shares come first
+        for (auto& p : h.peers) {
+            rt::for_each(p.cnt, HaloAdd{dev + p.lo, h.scratch.ptr() + p.scratch_off,
+                                        p.rank < g_rank});
+        }
+        return;
+    }
+#endif
+    // callback transport: the sum over all ranks is a superset
+    allreduce_sum(dev, h.n);
 }
 
 }  // namespace comm

@@ -25,6 +25,43 @@ public:
         m_prop->prepare(m_rin->out_shape());
         sanm_check(m_rout->nr_in() == m_prop->batch() * m_prop->out_elems(),
                    "remap_out input size does not match the function output");
+        // nodal index ranges the local tets read (x) and contribute to (b)
+        m_x_lo = m_nin;
+        m_x_hi = 0;
+        for (uint32_t c : m_rin->h_idx()) {
+            m_x_lo = std::min<uint64_t>(m_x_lo, c);
+            m_x_hi = std::max<uint64_t>(m_x_hi, (uint64_t)c + 1);
+        }
+        if (m_x_lo >= m_x_hi) m_x_lo = m_x_hi = 0;
+        const auto& rp = m_rout->h_rowptr();
+        m_b_lo = m_nout;
+        m_b_hi = 0;
+        for (uint64_t i = 0; i + 1 < rp.size(); ++i) {
+            if (rp[i + 1] > rp[i]) {
+                m_b_lo = std::min(m_b_lo, i);
+                m_b_hi = i + 1;
+            }
+        }
+        if (m_b_lo >= m_b_hi) m_b_lo = m_b_hi = 0;
+    }
+
+    /*! 0: all-reduce of the full right-hand sides (what the replicated solver
+     * needs; default).  1: nodal vectors stay distributed -- only the interface
+     * rows shared with neighbouring ranks are exchanged (comm::halo_sum), rows
+     * outside the local range [b_lo, b_hi) are left untouched, and
+     * run_host() transfers only the local ranges of x and b. */
+    void set_exchange(int mode) {
+        sanm_check(mode == 0 || mode == 1, "exchange mode %d", mode);
+        m_halo_mode = mode == 1;
+        if (m_halo_mode && !m_halo.ready) {
+            comm::halo_setup(m_halo, m_b_lo, m_b_hi, m_nout);
+        }
+    }
+    void local_ranges(uint64_t* r) const {
+        r[0] = m_x_lo;
+        r[1] = m_x_hi;
+        r[2] = m_b_lo;
+        r[3] = m_b_hi;
     }
 
     void set_x(const double* x) {
@@ -45,9 +82,12 @@ public:
         // kernels of an earlier sweep may still be reading m_x
         rt::pipe_wait(rt::PIPE_H2D, rt::fence_main());
         std::vector<void*> arrived(K + 1, nullptr);
+        // distributed mode: only what the local tets read / contribute to
+        const uint64_t xlo = m_halo_mode ? m_x_lo : 0, xhi = m_halo_mode ? m_x_hi : m_nin;
+        const uint64_t blo = m_halo_mode ? m_b_lo : 0, bhi = m_halo_mode ? m_b_hi : m_nout;
         for (int k = 0; k <= K; ++k) {
-            rt::pipe_h2d(m_x.ptr() + (size_t)k * m_nin, x + (size_t)k * m_nin,
-                         m_nin * sizeof(double));
+            rt::pipe_h2d(m_x.ptr() + (size_t)k * m_nin + xlo,
+                         x + (size_t)k * m_nin + xlo, (xhi - xlo) * sizeof(double));
             // x_K is never pushed (libsanm/anm.cpp:205-290: the last order
             // only produces its bias), but it is part of the caller's series
             arrived[k] = rt::fence_pipe(rt::PIPE_H2D);
@@ -59,9 +99,9 @@ public:
                 },
                 [&](int k) {
                     rt::pipe_wait(rt::PIPE_D2H, rt::fence_main());
-                    rt::pipe_d2h(b + (size_t)k * m_nout,
-                                 m_b.ptr() + (size_t)k * m_nout,
-                                 m_nout * sizeof(double));
+                    rt::pipe_d2h(b + (size_t)k * m_nout + blo,
+                                 m_b.ptr() + (size_t)k * m_nout + blo,
+                                 (bhi - blo) * sizeof(double));
                 });
         // x_K: nothing on the main stream waits for it; keep stream order sane
         for (void*& f : arrived) {
@@ -76,6 +116,14 @@ public:
     }
 
 private:
+    void exchange(double* b) {
+        if (m_halo_mode) {
+            comm::halo_sum(b, m_halo);
+        } else {
+            comm::allreduce_sum(b, m_nout);
+        }
+    }
+
     //! before_x(k): x_k is about to be read; after_b(k): b_k is complete
     template <typename BeforeX, typename AfterB>
     void run_impl(BeforeX&& before_x, AfterB&& after_b) {
@@ -88,7 +136,7 @@ private:
                 SANM_PROF("push_xi");
                 before_x(0);
                 p.push_xi_from(m_x.ptr(), m_b.ptr());
-                comm::allreduce_sum(m_b.ptr(), m_nout);
+                exchange(m_b.ptr());
                 after_b(0);
             }
             for (int k = 1; k <= K; ++k) {
@@ -98,7 +146,7 @@ private:
                     // the reference computes the per-tet Jacobian inside its
                     // first compute_next_order_bias (libsanm/symbolic.cpp:249-252)
                     if (k == 1) p.ensure_jacobian();
-                    comm::allreduce_sum(m_b.ptr() + (size_t)k * m_nout, m_nout);
+                    exchange(m_b.ptr() + (size_t)k * m_nout);
                     after_b(k);
                 }
                 if (k < K) {
@@ -120,7 +168,7 @@ private:
         {
             SANM_PROF("remap_out");
             m_rout->apply(m_b.ptr(), VecLayout{}, p.output_slot(0), soa_out);
-            comm::allreduce_sum(m_b.ptr(), m_nout);
+            exchange(m_b.ptr());
             after_b(0);
         }
         for (int k = 1; k <= K; ++k) {
@@ -132,7 +180,7 @@ private:
                 SANM_PROF("remap_out");
                 m_rout->apply(m_b.ptr() + (size_t)k * m_nout, VecLayout{},
                               p.output_slot(k), soa_out);
-                comm::allreduce_sum(m_b.ptr() + (size_t)k * m_nout, m_nout);
+                exchange(m_b.ptr() + (size_t)k * m_nout);
                 after_b(k);
             }
             if (k < K) {
@@ -170,6 +218,9 @@ private:
     std::shared_ptr<const Remap> m_rin, m_rout;
     int m_order;
     uint64_t m_nin = 0, m_nout = 0;
+    uint64_t m_x_lo = 0, m_x_hi = 0, m_b_lo = 0, m_b_hi = 0;
+    bool m_halo_mode = false;
+    comm::Halo m_halo;
     std::unique_ptr<TaylorProp> m_prop;
     rt::DBuf<double> m_x, m_b;
 };
@@ -203,6 +254,12 @@ int sanm_sweep_run(sanm_sweep_t* s) {
 }
 int sanm_sweep_run_host(sanm_sweep_t* s, const double* x, double* b) {
     return capi::guard([&] { s->s->run_host(x, b); });
+}
+int sanm_sweep_set_exchange(sanm_sweep_t* s, int mode) {
+    return capi::guard([&] { s->s->set_exchange(mode); });
+}
+int sanm_sweep_local_ranges(sanm_sweep_t* s, uint64_t* ranges4) {
+    return capi::guard([&] { s->s->local_ranges(ranges4); });
 }
 int sanm_sweep_get_b(sanm_sweep_t* s, double* b) {
     return capi::guard([&] { s->s->get_b(b); });

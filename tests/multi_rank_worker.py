@@ -57,6 +57,18 @@ def main():
         sw.set_x(x)
         sw.run()
         out[f"sweep_b_{energy}"] = sw.get_b()
+        # distributed nodal vectors: halo sums instead of the all-reduce; the
+        # local range must carry the same bits (also through run_host, which
+        # moves the local ranges only)
+        full = out[f"sweep_b_{energy}"]
+        sw.set_exchange(1)
+        xlo, xhi, blo, bhi = sw.local_ranges()
+        assert 0 <= xlo < xhi <= x.shape[1] and 0 <= blo < bhi <= full.shape[1]
+        sw.run()
+        assert np.array_equal(sw.get_b()[:, blo:bhi], full[:, blo:bhi]), energy
+        got = sw.run_host(x, np.zeros_like(full))
+        assert np.array_equal(got[:, blo:bhi], full[:, blo:bhi]), energy
+        out[f"sweep_range_{energy}"] = np.array([xlo, xhi, blo, bhi])
     np.savez(os.environ["OUT"] + f".rank{rank}.npz", **out)
     sdist.finalize_comm(b)
     dist.destroy_process_group()
