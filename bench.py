@@ -121,7 +121,35 @@ class ClockSampler(threading.Thread):
         self.samples = []
         self._stop_evt = threading.Event()
 
+    def _run_nvml(self) -> bool:
+        """NVML directly (5 ms period): nvidia-smi takes ~100 ms per call, longer
+        than a short timed region"""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons",
+                                  None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            bits = [(0x08, "hw_slowdown"), (0x40, "hw_thermal_slowdown"),
+                    (0x20, "sw_thermal_slowdown"), (0x04, "sw_power_cap")]
+        except Exception:
+            return False
+        while not self._stop_evt.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                r = int(get_reasons(h))
+                self.samples.append(
+                    [str(mhz), str(mx), "0"] +
+                    ["Active" if r & bit else "Not Active" for bit, _ in bits])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.005)
+        return True
+
     def run(self):
+        if self._run_nvml():
+            return
         while not self._stop_evt.is_set():
             try:
                 out = subprocess.run(

@@ -360,8 +360,8 @@ AnmSolver::AnmSolver(Kind kind, std::shared_ptr<const Graph> graph, int f,
     sanm_check(hyper.order >= 2 && m_rin && m_rout, "order=%d", hyper.order);
     sanm_check(hyper.order <= taylor::MAX_ORDER, "order %d above %d",
                hyper.order, taylor::MAX_ORDER);
-    sanm_check(!hyper.xcoeff_l2_penalty,
-               "xcoeff_l2_penalty is not implemented on the device path");
+    sanm_check(hyper.xcoeff_l2_penalty >= 0, "xcoeff_l2_penalty=%g",
+               hyper.xcoeff_l2_penalty);
     if (kind == IMPLICIT) {
         // libsanm/anm.cpp:501-507
         sanm_check(m_rin->in_shape().rank == 1 && m_rout->out_shape().rank == 1 &&
@@ -419,6 +419,16 @@ AnmSolver::AnmSolver(Kind kind, std::shared_ptr<const Graph> graph, int f,
 }
 
 AnmSolver::~AnmSolver() = default;
+
+void AnmSolver::lu_solve(double* x, const double* b) {
+    if (m_neq) {
+        // libsanm/sparse_solver.cpp:163-175: right-hand side K'b
+        m_neq->apply_transposed(m_d_kvals.ptr(), b, m_d_atb.ptr());
+        m_lu.solve(x, m_d_atb.ptr());
+    } else {
+        m_lu.solve(x, b);
+    }
+}
 
 void AnmSolver::dot_to(int slot, const double* a, const double* b, uint64_t n) {
     const uint64_t nblk = (n + DOT_CHUNK - 1) / DOT_CHUNK;
@@ -562,8 +572,18 @@ void AnmSolver::solve_expansion_coeffs() {
                             m_rin_e, m_rout_e});
                     {
                         SANM_PROF("lu_analyze_host");
-                        m_lu.analyze(n, m_kasm->rowptr().data(),
-                                     m_kasm->colidx().data());
+                        if (m_hyper.xcoeff_l2_penalty) {
+                            // libsanm/sparse_solver.cpp:366-395: factor K'K + p I
+                            m_neq.reset(new NormalEquations);
+                            m_neq->analyze(n, m_kasm->rowptr(), m_kasm->colidx());
+                            m_lu.analyze(n, m_neq->rowptr2().data(),
+                                         m_neq->colidx2().data());
+                            m_d_k2vals.alloc(m_neq->nnz2());
+                            m_d_atb.alloc(n);
+                        } else {
+                            m_lu.analyze(n, m_kasm->rowptr().data(),
+                                         m_kasm->colidx().data());
+                        }
                     }
                     m_d_kvals.alloc(m_kasm->nnz());
                     if (fio && m_prop->jacobian_pitch()) {
@@ -599,11 +619,17 @@ void AnmSolver::solve_expansion_coeffs() {
             }
             {
                 SANM_PROF("sparse_prep");
-                m_lu.factor(m_d_kvals.ptr());
+                if (m_neq) {
+                    m_neq->form(m_d_kvals.ptr(), m_hyper.xcoeff_l2_penalty,
+                                m_d_k2vals.ptr());
+                    m_lu.factor(m_d_k2vals.ptr());
+                } else {
+                    m_lu.factor(m_d_kvals.ptr());
+                }
             }
             {
                 SANM_PROF("sparse_solve");
-                m_lu.solve(m_d_xgt.ptr(), grad_t);
+                lu_solve(m_d_xgt.ptr(), grad_t);
             }
             dot_to(SC_DOT, m_d_xgt.ptr(), m_d_xgt.ptr(), n);
             rt::for_each(1, ScalarT1{sc});
@@ -618,13 +644,13 @@ void AnmSolver::solve_expansion_coeffs() {
             reduce(m_d_bi.ptr(), n);
             {
                 SANM_PROF("sparse_solve");
-                m_lu.solve(m_d_xbi.ptr(), m_d_bi.ptr());
+                lu_solve(m_d_xbi.ptr(), m_d_bi.ptr());
             }
             dot_to(SC_DOT, m_d_xbi.ptr(), x1, n);
             rt::for_each(1, ScalarTi{sc});
             rt::for_each(n + 1, CombineX{xti, m_d_xgt.ptr(), m_d_xbi.ptr(), sc, n});
         }
-        if (m_hyper.sanity_check) {
+        if (m_hyper.sanity_check && !m_hyper.xcoeff_l2_penalty) {
             // libsanm/anm.cpp:266-285, evaluated after the loop
             SANM_PROF("anm_sanity_check");
             m_lu.apply(m_d_tmp.ptr(), xti);
@@ -662,7 +688,7 @@ void AnmSolver::solve_expansion_coeffs() {
                        (size_t)(i / m_ld));
         }
     }
-    if (m_hyper.sanity_check) {
+    if (m_hyper.sanity_check && !m_hyper.xcoeff_l2_penalty) {
         std::vector<double> chk(2 * (K + 2));
         rt::d2h(chk.data(), sc + SC_CHECK0, chk.size() * sizeof(double));
         for (int i = 1; i <= K; ++i) {

@@ -15,6 +15,7 @@
 #include "graph.h"
 #include "pade.h"
 #include "remap.h"
+#include "normal_eq.h"
 #include "sparse_lu.h"
 #include "taylor.h"
 
@@ -179,6 +180,11 @@ private:
     rt::DBuf<double> m_d_y;    //!< EQN: y
     rt::DBuf<double> m_d_grad_t, m_d_bi, m_d_xbi, m_d_xgt, m_d_fx, m_d_tmp;
     rt::DBuf<double> m_d_kvals;
+    //! xcoeff_l2_penalty != 0: the factor is of K'K + p I (normal_eq.h)
+    std::unique_ptr<NormalEquations> m_neq;
+    rt::DBuf<double> m_d_k2vals, m_d_atb;
+    //! x = K^-1 b, or the Tikhonov solution when the penalty is set
+    void lu_solve(double* x, const double* b);
     rt::DBuf<double> m_d_sc;   //!< device scalars
     rt::DBuf<double> m_d_partial;
 

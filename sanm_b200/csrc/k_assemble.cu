@@ -17,6 +17,10 @@
 #include "prof.h"
 
 #include <algorithm>
+#include <omp.h>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 namespace sanm_b200 {
 
@@ -98,6 +102,16 @@ std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
     if ((uint64_t)KE_ENTRIES * npad >= (1ull << 32)) return nullptr;
     const uint64_t nnz = k_rowptr[n];
     if (nnz + n >= (1ull << 32) || io.nout != n) return nullptr;
+    const bool dbg = getenv("SANM_LU_DEBUG") != nullptr;
+    auto tnow = [] { return std::chrono::steady_clock::now(); };
+    auto t_start = tnow();
+    auto lap = [&](const char* what) {
+        if (!dbg) return;
+        auto t1 = tnow();
+        printf("[k-lists] %-28s %8.2f ms\n", what,
+               std::chrono::duration<double, std::milli>(t1 - t_start).count());
+        t_start = t1;
+    };
     std::vector<uint8_t> tab((size_t)27 * npad, 0);
     std::vector<uint32_t> dloc((size_t)KE_ENTRIES * N, NONE32);
     bool bad = false;
@@ -157,23 +171,43 @@ std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
             }
         }
     }
+    lap("dloc (parallel)");
     if (bad) return nullptr;
-    // source lists per destination, ascending (tet, local entry)
-    std::vector<uint32_t> kptr(nnz + n + 1, 0);
-    for (size_t i = 0; i < dloc.size(); ++i) {
-        if (dloc[i] != NONE32) ++kptr[dloc[i] + 1];
+    // source lists per destination, ascending (tet, local entry): a counting
+    // sort, parallel over destination ranges (every thread scans all of dloc
+    // and keeps what falls into its range, so the order inside a list is the
+    // scan order whatever the thread count)
+    const uint64_t nd = nnz + n;
+    std::vector<uint32_t> kptr(nd + 1, 0);
+    const int T = rt::host_threads();
+#pragma omp parallel num_threads(T)
+    {
+        const int t = omp_get_thread_num(), nt = omp_get_num_threads();
+        const uint32_t d0 = (uint32_t)(nd * t / nt), d1 = (uint32_t)(nd * (t + 1) / nt);
+        for (size_t i = 0; i < dloc.size(); ++i) {
+            const uint32_t d = dloc[i];
+            if (d >= d0 && d < d1) ++kptr[d + 1];  // NONE32 is out of every range
+        }
     }
-    for (uint64_t p = 0; p < nnz + n; ++p) kptr[p + 1] += kptr[p];
-    std::vector<uint32_t> ksrc(kptr[nnz + n]);
+    lap("count");
+    for (uint64_t p = 0; p < nd; ++p) kptr[p + 1] += kptr[p];
+    std::vector<uint32_t> ksrc(kptr[nd]);
     {
         std::vector<uint32_t> fill(kptr.begin(), kptr.end() - 1);
-        for (uint64_t e = 0; e < N; ++e) {
-            for (int l = 0; l < KE_ENTRIES; ++l) {
-                const uint32_t d = dloc[(size_t)e * KE_ENTRIES + l];
-                if (d != NONE32) ksrc[fill[d]++] = (uint32_t)((uint64_t)l * npad + e);
+#pragma omp parallel num_threads(T)
+        {
+            const int t = omp_get_thread_num(), nt = omp_get_num_threads();
+            const uint32_t d0 = (uint32_t)(nd * t / nt), d1 = (uint32_t)(nd * (t + 1) / nt);
+            for (uint64_t e = 0; e < N; ++e) {
+                const uint32_t* row = dloc.data() + (size_t)e * KE_ENTRIES;
+                for (int l = 0; l < KE_ENTRIES; ++l) {
+                    const uint32_t d = row[l];
+                    if (d >= d0 && d < d1) ksrc[fill[d]++] = (uint32_t)((uint64_t)l * npad + e);
+                }
             }
         }
     }
+    lap("fill");
     auto ret = std::unique_ptr<FusedKAssembly>(new FusedKAssembly);
     ret->m_n_tets = N;
     ret->m_npad = npad;
@@ -183,6 +217,7 @@ std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
     ret->m_kptr.upload(kptr);
     ret->m_ksrc.upload(ksrc);
     ret->m_cbuf.alloc((size_t)KE_ENTRIES * npad);
+    lap("upload");
     return ret;
 }
 

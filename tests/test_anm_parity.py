@@ -71,6 +71,20 @@ def test_pow(impl, ref):
                    lambda x: x ** e)
 
 
+def test_xcoeff_l2_penalty(impl, ref):
+    """xcoeff_l2_penalty: the tangent systems are solved as Tikhonov normal
+    equations (K'K + p I) x = K'b (libsanm/anm.cpp:241,
+    sparse_solver.cpp:366-395,163-175); series and solution must follow the
+    oracle, which takes the same path"""
+    rng = np.random.default_rng(11)
+    x0 = rng.uniform(0.8, 1.6, (6, 3, 3)) * np.eye(3)[None] + \
+        rng.uniform(-0.05, 0.05, (6, 3, 3))
+    hyper = Hyper(order=8, xcoeff_l2_penalty=1e-6, solution_check_tol=1e-2)
+    check_case(impl, ref,
+               lambda g: (lambda x: x.batched_matmul(x))(g.placeholder()), x0,
+               lambda x: x @ x, t_dst=1.5, hyper=hyper, sol_tol=1e-6)
+
+
 def test_matinvmul(impl, ref):
     """Symbolic.MatInvMul, tests/symbolic.cpp:179-233"""
     rng = np.random.default_rng(1)
