@@ -47,19 +47,52 @@ PadeApproximation::PadeApproximation(std::vector<const double*> xs, size_t len,
 
     // modified Gram-Schmidt of x_1..x_n (pade.cpp:30-55)
     std::vector<std::vector<double>> orth(nx);
+    // Per i: all projections a(i, j) in ONE pass over x_i (they use the
+    // original x_i, so they do not depend on each other), then one pass that
+    // subtracts them in the order j = 1, 2, ...  Chunking and summation orders
+    // are those of dot() above, so the numbers are the ones of the plain
+    // j-by-j loop; only the number of parallel regions drops from O(n^2) to
+    // O(n) (they cost more than the arithmetic on a 22 k-vector).
+    constexpr size_t CHUNK = 4096;
+    const size_t nchunk = (len + CHUNK - 1) / CHUNK;
+    const bool par = nchunk > 1;
+    std::vector<double> part((size_t)nx * std::max<size_t>(nchunk, 1));
     for (int i = 1; i <= n; ++i) {
         auto& u = orth[i];
         u.assign(m_xs[i], m_xs[i] + len);
-        for (int j = 1; j < i; ++j) {
-            a(i, j) = dot(m_xs[i], orth[j].data(), len);
-            if (anm_cond && j == 1) {
-                sanm_check(std::fabs(a(i, j)) < 1e-4);
-                a(i, j) = 0;
-            } else {
-                const double f = -a(i, j);
-                const double* o = orth[j].data();
-#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
-                for (int64_t q = 0; q < (int64_t)len; ++q) u[q] += o[q] * f;
+        if (i > 1) {
+            const double* xi = m_xs[i];
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (par)
+            for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
+                const size_t i0 = c * CHUNK, i1 = std::min(len, i0 + CHUNK);
+                for (int j = 1; j < i; ++j) {
+                    const double* o = orth[j].data();
+                    double sacc = 0;
+                    for (size_t q = i0; q < i1; ++q) sacc += xi[q] * o[q];
+                    part[(size_t)j * nchunk + c] = sacc;
+                }
+            }
+            std::vector<double> fac(i, 0.0);
+            for (int j = 1; j < i; ++j) {
+                double sacc = 0;
+                for (size_t c = 0; c < nchunk; ++c) sacc += part[(size_t)j * nchunk + c];
+                a(i, j) = sacc;
+                if (anm_cond && j == 1) {
+                    sanm_check(std::fabs(a(i, j)) < 1e-4);
+                    a(i, j) = 0;
+                } else {
+                    fac[j] = -a(i, j);
+                }
+            }
+            const int j_first = anm_cond ? 2 : 1;
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (par)
+            for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
+                const size_t i0 = c * CHUNK, i1 = std::min(len, i0 + CHUNK);
+                for (int j = j_first; j < i; ++j) {
+                    const double* o = orth[j].data();
+                    const double f = fac[j];
+                    for (size_t q = i0; q < i1; ++q) u[q] += o[q] * f;
+                }
             }
         }
         double aii = std::sqrt(dot(u.data(), u.data(), len));
@@ -111,13 +144,18 @@ PadeApproximation::PadeApproximation(std::vector<const double*> xs, size_t len,
 std::vector<double> PadeApproximation::eval_nume(double a, const double* d,
                                                  int n) const {
     // pade.cpp:187-194
-    std::vector<double> sum(m_len, 0.0);
-    for (int i = n; i >= 1; --i) {
-        double scale = poly::eval(d, n - i + 1, a);
-        const double* x = m_xs[i];
-#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
-        for (int64_t q = 0; q < (int64_t)m_len; ++q) {
-            sum[q] = sum[q] * a + x[q] * scale;
+    std::vector<double> sum(m_len, 0.0), scale(n + 1, 0.0);
+    for (int i = n; i >= 1; --i) scale[i] = poly::eval(d, n - i + 1, a);
+    constexpr int64_t CHUNK = 4096;
+    const int64_t nchunk = ((int64_t)m_len + CHUNK - 1) / CHUNK;
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (nchunk > 1)
+    for (int64_t c = 0; c < nchunk; ++c) {
+        const int64_t q0 = c * CHUNK, q1 = std::min<int64_t>(m_len, q0 + CHUNK);
+        // Horner per element, i = n .. 1 (same operation order as a pass per i)
+        for (int i = n; i >= 1; --i) {
+            const double* x = m_xs[i];
+            const double sc = scale[i];
+            for (int64_t q = q0; q < q1; ++q) sum[q] = sum[q] * a + x[q] * sc;
         }
     }
     return sum;
@@ -143,17 +181,49 @@ bool PadeApproximation::estimate_valid_range(double start, double eps,
 
     const double eps2 = eps * eps;
     const int n = (int)m_xs.size() - 2;
+    // One fused pass per candidate: both numerators by Horner (x_i read once
+    // for the two), their weighted difference and the two squared norms.  The
+    // element operations and the chunked summation are those of eval_nume() +
+    // dot(), so the decision is the one of the unfused form.
+    constexpr int64_t CHUNK = 4096;
+    const int64_t nchunk = ((int64_t)m_len + CHUNK - 1) / CHUNK;
+    std::vector<double> part_d(nchunk), part_n(nchunk), sc_n(n + 1), sc_l(n + 1);
     auto check = [&](double a) {
         double denom_n = poly::eval(m_d, a), denom_lo = poly::eval(m_d_lo, a);
-        std::vector<double> pn = eval_nume(a, m_d.data(), n),
-                            pl = eval_nume(a, m_d_lo.data(), n - 1);
         const double f = denom_n / denom_lo;
-        // same fixed chunking as dot()
-        std::vector<double> dv(m_len);
-#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static)
-        for (int64_t q = 0; q < (int64_t)m_len; ++q) dv[q] = pl[q] * f - pn[q];
-        const double diff2 = dot(dv.data(), dv.data(), m_len),
-                     pn2 = dot(pn.data(), pn.data(), m_len);
+        for (int i = n; i >= 1; --i) sc_n[i] = poly::eval(m_d.data(), n - i + 1, a);
+        for (int i = n - 1; i >= 1; --i) sc_l[i] = poly::eval(m_d_lo.data(), n - 1 - i + 1, a);
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (nchunk > 1)
+        for (int64_t c = 0; c < nchunk; ++c) {
+            const int64_t q0 = c * CHUNK, q1 = std::min<int64_t>(m_len, q0 + CHUNK);
+            double pn[64], pl[64];
+            double sd = 0, sn = 0;
+            for (int64_t qb = q0; qb < q1; qb += 64) {
+                const int w = (int)std::min<int64_t>(64, q1 - qb);
+                for (int t = 0; t < w; ++t) pn[t] = pl[t] = 0.0;
+                for (int i = n; i >= 1; --i) {
+                    const double* x = m_xs[i] + qb;
+                    const double s1 = sc_n[i];
+                    for (int t = 0; t < w; ++t) pn[t] = pn[t] * a + x[t] * s1;
+                    if (i <= n - 1) {
+                        const double s2 = sc_l[i];
+                        for (int t = 0; t < w; ++t) pl[t] = pl[t] * a + x[t] * s2;
+                    }
+                }
+                for (int t = 0; t < w; ++t) {
+                    const double dv = pl[t] * f - pn[t];
+                    sd += dv * dv;
+                    sn += pn[t] * pn[t];
+                }
+            }
+            part_d[c] = sd;
+            part_n[c] = sn;
+        }
+        double diff2 = 0, pn2 = 0;
+        for (int64_t c = 0; c < nchunk; ++c) {
+            diff2 += part_d[c];
+            pn2 += part_n[c];
+        }
         return diff2 <= pn2 * eps2;
     };
     double left = start * 1.001, right = start + (pole - start) * 0.99;
