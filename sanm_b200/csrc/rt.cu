@@ -103,6 +103,17 @@ void set_stream(void* s) {
 
 void sync() { SANM_CUDA_CHECK(cudaStreamSynchronize(stream())); }
 
+int sm_count() {
+    static const int n = [] {
+        check_device();
+        int dev = 0, v = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        return v > 0 ? v : 1;
+    }();
+    return n;
+}
+
 void* dmalloc(size_t bytes) {
     check_device();
     void* p = nullptr;

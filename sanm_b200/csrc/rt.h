@@ -35,8 +35,32 @@
 #include <cmath>
 #else
 #include <cuda_runtime.h>
+#include <cooperative_groups.h>
 #define SANM_HD __host__ __device__
 #define SANM_D __device__
+#endif
+
+//! compiler-only barrier: loads written before it are issued before any
+//! arithmetic written after it (memory-level parallelism by construction)
+#define SANM_LOADS_ISSUED() asm volatile("" ::: "memory")
+//! read-only global load (ld.global.nc): for data no kernel writes while it
+//! runs.  Besides the cache policy this tells ptxas the access is GLOBAL:
+//! pointers fetched from descriptors are generic, and generic loads are kept
+//! in program order next to their uses instead of being issued together.
+#ifdef __CUDA_ARCH__
+#define SANM_LDG(p) __ldg(p)
+#else
+#define SANM_LDG(p) (*(p))
+#endif
+//! the same for loads the compiler may treat as invariant (const __restrict__):
+//! an empty instruction that consumes and redefines 8 loaded doubles, so all
+//! 8 loads are issued before the first use
+#ifdef __CUDA_ARCH__
+#define SANM_TIE8(a)                                                         \
+    asm volatile("" : "+d"(a[0]), "+d"(a[1]), "+d"(a[2]), "+d"(a[3]),         \
+                      "+d"(a[4]), "+d"(a[5]), "+d"(a[6]), "+d"(a[7]))
+#else
+#define SANM_TIE8(a) (void)0
 #endif
 
 namespace sanm_b200 {
@@ -228,12 +252,12 @@ void for_each(size_t n, const F& f) {
 
 struct BlockCtx {
     int tid = 0, nthr = 1;
-    size_t bid = 0;
+    size_t bid = 0, nblk = 1;
     char* smem = nullptr;
     void sync() const {}
 };
 
-template <class F>
+template <int MAXT = 0, class F>
 void for_each_block(size_t nblocks, int /*threads*/, size_t smem_bytes,
                     const F& f) {
     count_launch();
@@ -241,8 +265,31 @@ void for_each_block(size_t nblocks, int /*threads*/, size_t smem_bytes,
     for (size_t b = 0; b < nblocks; ++b) {
         BlockCtx c;
         c.bid = b;
+        c.nblk = nblocks;
         c.smem = sm.data();
         f(c);
+    }
+}
+
+/*! Persistent launch: a fixed grid of co-resident blocks runs f(c, phase) for
+ * phase = 0 .. nphases-1 with a grid-wide barrier (and memory fence) between
+ * phases; inside a phase the blocks share the work by striding over it with
+ * c.bid / c.nblk.  Replaces a chain of dependent kernel launches.  Host
+ * build: three emulated blocks, phases as plain loops. */
+template <int MAXT = 1024, class F>
+void for_each_block_phased(int /*threads*/, size_t smem_bytes, uint32_t nphases,
+                           const F& f) {
+    count_launch();
+    std::vector<char> sm(smem_bytes + 16);
+    constexpr size_t NBLK = 3;
+    for (uint32_t p = 0; p < nphases; ++p) {
+        for (size_t b = 0; b < NBLK; ++b) {
+            BlockCtx c;
+            c.bid = b;
+            c.nblk = NBLK;
+            c.smem = sm.data();
+            f(c, p);
+        }
     }
 }
 #else
@@ -264,34 +311,106 @@ void for_each(size_t n, const F& f) {
 
 struct BlockCtx {
     int tid, nthr;
-    size_t bid;
+    size_t bid, nblk;
     char* smem;
     __device__ void sync() const { __syncthreads(); }
 };
 
+/* MAXT = compile-time bound of the block size (__launch_bounds__).  It matters
+ * beyond register allocation: without it ptxas schedules for 1024-thread
+ * blocks and serialises independent global loads (load, use, load, use ...)
+ * even where the PTX issues them back to back, which turns every latency-
+ * bound kernel of the solver into a chain of memory round trips. */
 template <class F>
-__global__ void k_for_each_block(F f) {
+__device__ __forceinline__ void run_block(F& f) {
     extern __shared__ __align__(16) char smem_raw[];
     BlockCtx c;
     c.tid = threadIdx.x;
     c.nthr = blockDim.x;
     c.bid = blockIdx.x;
+    c.nblk = gridDim.x;
     c.smem = smem_raw;
     f(c);
 }
+//! MAXT = 0: no bound (the register-heavy element kernels size themselves)
+template <class F, int MAXT>
+__global__ void k_for_each_block(F f) {
+    run_block(f);
+}
+//! bounded, and "one block per SM is enough": lets ptxas spend registers on
+//! keeping loads in flight
+template <class F, int MAXT>
+__global__ void __launch_bounds__(MAXT > 0 ? MAXT : 1024, 1) k_for_each_block_b(F f) {
+    run_block(f);
+}
 
-template <class F>
-void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
-                    const F& f) {
-    if (!nblocks) return;
+//! see the host build above; cooperative launch, grid = all co-resident blocks
+template <class F, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) k_phased(F f, uint32_t nphases) {
+    extern __shared__ __align__(16) char smem_raw[];
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    BlockCtx c;
+    c.tid = threadIdx.x;
+    c.nthr = blockDim.x;
+    c.bid = blockIdx.x;
+    c.nblk = gridDim.x;
+    c.smem = smem_raw;
+    for (uint32_t p = 0; p < nphases; ++p) {
+        f(c, p);
+        if (p + 1 < nphases) grid.sync();
+    }
+}
+
+int sm_count();
+
+template <int MAXT = 1024, class F>
+void for_each_block_phased(int threads, size_t smem_bytes, uint32_t nphases,
+                           const F& f) {
+    if (!nphases) return;
+    if (threads > MAXT) {
+        throw ::sanm_b200::Error{SANM_ERR_ASSERT, "block size above its bound"};
+    }
     count_launch();
     if (smem_bytes > 48 * 1024) {
         SANM_CUDA_CHECK(cudaFuncSetAttribute(
-                k_for_each_block<F>,
-                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+                k_phased<F, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                (int)smem_bytes));
     }
-    k_for_each_block<F>
-            <<<(unsigned)nblocks, threads, smem_bytes, stream()>>>(f);
+    int per_sm = 0;
+    SANM_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+            &per_sm, k_phased<F, MAXT>, threads, smem_bytes));
+    if (per_sm < 1) {
+        throw ::sanm_b200::Error{SANM_ERR_CUDA,
+                                 "persistent kernel does not fit on an SM"};
+    }
+    F fcopy = f;
+    uint32_t np = nphases;
+    void* args[] = {&fcopy, &np};
+    SANM_CUDA_CHECK(cudaLaunchCooperativeKernel(
+            (const void*)k_phased<F, MAXT>, dim3((unsigned)(per_sm * sm_count())),
+            dim3((unsigned)threads), args, smem_bytes, stream()));
+}
+
+template <int MAXT = 0, class F>
+void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
+                    const F& f) {
+    if (!nblocks) return;
+    if (MAXT > 0 && threads > MAXT) {
+        throw ::sanm_b200::Error{SANM_ERR_ASSERT, "block size above its bound"};
+    }
+    count_launch();
+    void (*kern)(F);
+    if constexpr (MAXT > 0) {
+        kern = k_for_each_block_b<F, MAXT>;
+    } else {
+        kern = k_for_each_block<F, MAXT>;
+    }
+    if (smem_bytes > 48 * 1024) {
+        SANM_CUDA_CHECK(cudaFuncSetAttribute(
+                kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                (int)smem_bytes));
+    }
+    kern<<<(unsigned)nblocks, threads, smem_bytes, stream()>>>(f);
     SANM_CUDA_CHECK(cudaGetLastError());
 }
 #endif

@@ -443,9 +443,13 @@ SANM_HD inline double solve_partial(const double* __restrict__ col0, uint64_t ld
         for (int u = 0; u < U; ++u) {
             const uint32_t jj = j + u * GROUPS;
             const bool ok = jj < ncol;
-            a[u] = ok ? col0[(uint64_t)jj * ld] : 0.0;
+            // the factors are read-only during a solve: ld.global.nc
+            a[u] = ok ? SANM_LDG(col0 + (uint64_t)jj * ld) : 0.0;
             x[u] = ok ? v[jj] : 0.0;
         }
+        // all U loads in flight before the first use (needs the bounded
+        // launch, see rt.h k_for_each_block_b)
+        SANM_TIE8(a);
 #pragma unroll
         for (int u = 0; u < U; ++u) acc[u] += a[u] * x[u];
     }
@@ -568,6 +572,60 @@ struct BackwardKernel {
     }
 };
 
+/* ---- the whole solve as ONE persistent launch: phase l < nlev is forward
+ * level l, phase nlev + m is backward level nlev-1-m; a grid-wide barrier
+ * (~1 us) between phases replaces 2 nlev dependent kernel launches.  Pays off
+ * on small systems, where a level is only a few blocks of work; larger ones
+ * run better as one launch per level, whose blocks have that level's shape. */
+struct LevelD {
+    uint32_t fwd_off, fwd_n, bwd_off, bwd_n;
+    uint32_t fwd_wide, bwd_wide;
+};
+
+struct SolvePhased {
+    const FrontD* fronts;
+    const uint32_t* gsrc;
+    const double* vecs;
+    const Task* fwd_tasks;
+    const Task* bwd_tasks;
+    const LevelD* levels;
+    uint32_t nlev;
+    const double* b;
+    const uint32_t* perm;
+    double* xp;
+    double* x;
+    SANM_D void operator()(const rt::BlockCtx& c, uint32_t phase) const {
+        rt::BlockCtx c2 = c;
+        if (phase < nlev) {
+            const LevelD L = levels[phase];
+            for (size_t t = c.bid; t < L.fwd_n; t += c.nblk) {
+                c2.bid = t;
+                if (L.fwd_wide) {
+                    ForwardKernel<FWD_ROWS, FWD_GROUPS_WIDE>{
+                            fronts, gsrc, vecs, fwd_tasks + L.fwd_off, b, perm}(c2);
+                } else {
+                    ForwardKernel<FWD_ROWS, FWD_GROUPS_NARROW>{
+                            fronts, gsrc, vecs, fwd_tasks + L.fwd_off, b, perm}(c2);
+                }
+                c.sync();  // shared memory is reused by the next task
+            }
+        } else {
+            const LevelD L = levels[2 * nlev - 1 - phase];
+            for (size_t t = c.bid; t < L.bwd_n; t += c.nblk) {
+                c2.bid = t;
+                if (L.bwd_wide) {
+                    BackwardKernel<BWD_ROWS, BWD_GROUPS_WIDE>{
+                            fronts, bwd_tasks + L.bwd_off, xp, x, perm}(c2);
+                } else {
+                    BackwardKernel<BWD_ROWS, BWD_GROUPS_NARROW>{
+                            fronts, bwd_tasks + L.bwd_off, xp, x, perm}(c2);
+                }
+                c.sync();
+            }
+        }
+    }
+};
+
 struct SpmvKernel {
     const uint32_t* rowptr;
     const uint32_t* colidx;
@@ -604,6 +662,8 @@ struct SparseLU::Impl {
     };
     std::vector<Level> levels;
     rt::DBuf<Task> asm_tasks, fwd_tasks, bwd_tasks;
+    rt::DBuf<LevelD> level_d;
+    size_t solve_smem = 0;
     rt::DBuf<uint32_t> small_list, big_list;
     bool factored = false;
 };
@@ -746,6 +806,23 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         L.fwd_n = (uint32_t)fwd_t.size() - L.fwd_off;
         L.bwd_n = (uint32_t)bwd_t.size() - L.bwd_off;
     }
+    {
+        std::vector<LevelD> ld(nlev);
+        size_t sm = 0;
+        for (uint32_t l = 0; l < nlev; ++l) {
+            const auto& L = I.levels[l];
+            const bool fw = L.max_nc >= SOLVE_WIDE_COLS, bw = L.max_nr >= SOLVE_WIDE_COLS;
+            ld[l] = {L.fwd_off, L.fwd_n, L.bwd_off, L.bwd_n, fw, bw};
+            sm = std::max(sm, 2 * (size_t)L.max_nc +
+                                      (fw ? solve_scratch_doubles<FWD_ROWS, FWD_GROUPS_WIDE>()
+                                          : solve_scratch_doubles<FWD_ROWS, FWD_GROUPS_NARROW>()));
+            sm = std::max(sm, (size_t)L.max_nr +
+                                      (bw ? solve_scratch_doubles<BWD_ROWS, BWD_GROUPS_WIDE>()
+                                          : solve_scratch_doubles<BWD_ROWS, BWD_GROUPS_NARROW>()));
+        }
+        I.level_d.upload(ld);
+        I.solve_smem = sm * sizeof(double);
+    }
     I.asm_tasks.upload(asm_t);
     I.fwd_tasks.upload(fwd_t);
     I.bwd_tasks.upload(bwd_t);
@@ -795,10 +872,10 @@ void SparseLU::factor(const double* vals_dev) {
     I.fronts.zero();
     I.counters.zero();
     // max |a_ij| (scale of the static pivot threshold): two stages
-    rt::for_each_block(ABSMAX_BLOCKS, 256, 256 * sizeof(double),
+    rt::for_each_block<256>(ABSMAX_BLOCKS, 256, 256 * sizeof(double),
                        AbsMaxKernel{I.vals.ptr(), m_nnz, ABSMAX_BLOCKS,
                                     I.scal.ptr() + 4});
-    rt::for_each_block(1, 256, 256 * sizeof(double),
+    rt::for_each_block<256>(1, 256, 256 * sizeof(double),
                        AbsMaxKernel{I.scal.ptr() + 4, ABSMAX_BLOCKS, 1,
                                     I.scal.ptr()});
     rt::for_each(m_nnz, ScatterA{I.fronts.ptr(), I.a_dest.ptr(), I.vals.ptr()});
@@ -807,14 +884,14 @@ void SparseLU::factor(const double* vals_dev) {
     for (auto& L : I.levels) {
         if (L.asm_n) {
             LuScope ps{"lu_asm"};
-            rt::for_each_block(L.asm_n, 256, 0,
+            rt::for_each_block<256>(L.asm_n, 256, 0,
                                AssembleChildren{I.fd.ptr(), I.child_list.ptr(),
                                                 I.asm_tasks.ptr() + L.asm_off});
         }
         if (L.small_n) {
             size_t smem = (size_t)L.small_max_nr * L.small_max_nr * sizeof(double) + 16;
             LuScope ps{"lu_small"};
-            rt::for_each_block(L.small_n, 256, smem,
+            rt::for_each_block<256>(L.small_n, 256, smem,
                                SmallFrontKernel{I.fd.ptr(),
                                                 I.small_list.ptr() + L.small_off,
                                                 amax, npert});
@@ -826,26 +903,26 @@ void SparseLU::factor(const double* vals_dev) {
                 {
                     LuScope ps{"lu_diag"};
                     // 4 warps per front (gj32.cuh)
-                    rt::for_each_block(
+                    rt::for_each_block<128>(
                             L.big_n, 128,
                             (NB * NB + 2 * NB) * sizeof(double) + NB * sizeof(uint32_t) + 16,
                             BigDiagKernel{I.fd.ptr(), list, kb, amax, npert});
                 }
                 {
                     LuScope ps{"lu_row"};
-                    rt::for_each_block((size_t)L.big_n * tiles, 256,
+                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256,
                                        (NB * NB + NB * 64) * sizeof(double),
                                        BigRowPanelKernel{I.fd.ptr(), list, kb, tiles});
                 }
                 {
                     LuScope ps{"lu_gemm"};
-                    rt::for_each_block((size_t)L.big_n * tiles * tiles, 256,
+                    rt::for_each_block<256>((size_t)L.big_n * tiles * tiles, 256,
                                        2 * NB * 64 * sizeof(double),
                                        BigGemmKernel{I.fd.ptr(), list, kb, tiles});
                 }
                 {
                     LuScope ps{"lu_col"};
-                    rt::for_each_block((size_t)L.big_n * tiles, 256,
+                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256,
                                        (NB * NB + NB * 64) * sizeof(double),
                                        BigColPanelKernel{I.fd.ptr(), list, kb, tiles});
                 }
@@ -860,6 +937,16 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
     sanm_check(I.factored, "solve() before factor()");
     // b may alias x: the forward sweep has consumed b before the backward
     // sweep writes x
+    static const bool per_level = getenv("SANM_LU_PER_LEVEL") != nullptr;
+    if (!per_level && !g_lu_prof && m_n <= 12000) {
+        const uint32_t nlev = (uint32_t)I.levels.size();
+        rt::for_each_block_phased<512>(
+                512, I.solve_smem, 2 * nlev,
+                SolvePhased{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
+                            I.fwd_tasks.ptr(), I.bwd_tasks.ptr(), I.level_d.ptr(),
+                            nlev, b_dev, I.perm.ptr(), I.xp.ptr(), x_dev});
+        return;
+    }
     char tag[32];
     for (auto& L : I.levels) {
         snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - I.levels.data()));
@@ -867,7 +954,7 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
         constexpr int R = FWD_ROWS;
         if (L.max_nc >= SOLVE_WIDE_COLS) {
             constexpr int G = FWD_GROUPS_WIDE;
-            rt::for_each_block(
+            rt::for_each_block<R * G>(
                     L.fwd_n, R * G,
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
                     ForwardKernel<R, G>{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
@@ -875,7 +962,7 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
                                      I.perm.ptr()});
         } else {
             constexpr int G = FWD_GROUPS_NARROW;
-            rt::for_each_block(
+            rt::for_each_block<R * G>(
                     L.fwd_n, R * G,
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
                     ForwardKernel<R, G>{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
@@ -890,14 +977,14 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
         constexpr int R = BWD_ROWS;
         if (L.max_nr >= SOLVE_WIDE_COLS) {
             constexpr int G = BWD_GROUPS_WIDE;
-            rt::for_each_block(
+            rt::for_each_block<R * G>(
                     L.bwd_n, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
                     BackwardKernel<R, G>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
                                       I.xp.ptr(), x_dev, I.perm.ptr()});
         } else {
             constexpr int G = BWD_GROUPS_NARROW;
-            rt::for_each_block(
+            rt::for_each_block<R * G>(
                     L.bwd_n, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
                     BackwardKernel<R, G>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
