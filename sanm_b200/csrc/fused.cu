@@ -345,6 +345,9 @@ void FusedProp::launch_step(int k_push, int kb, bool want_out, const double* x) 
         }
     } else {
         SANM_PROF("k_fused_step");
+        // unbounded launch on purpose: with __launch_bounds__(128, 1) ptxas takes
+        // 255 registers (2.42 -> 1.76 G tet*order/s), with (128, 3) it trades
+        // ILP for occupancy (2.24 G); its own choice of 166-240 is the best
         if (use_io) {
             rt::for_each_block(
                     ntiles, TILE, smem,

@@ -257,7 +257,7 @@ struct BlockCtx {
     void sync() const {}
 };
 
-template <int MAXT = 0, class F>
+template <int MAXT = 0, int MINB = 1, class F>
 void for_each_block(size_t nblocks, int /*threads*/, size_t smem_bytes,
                     const F& f) {
     count_launch();
@@ -339,8 +339,8 @@ __global__ void k_for_each_block(F f) {
 }
 //! bounded, and "one block per SM is enough": lets ptxas spend registers on
 //! keeping loads in flight
-template <class F, int MAXT>
-__global__ void __launch_bounds__(MAXT > 0 ? MAXT : 1024, 1) k_for_each_block_b(F f) {
+template <class F, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT > 0 ? MAXT : 1024, MINB) k_for_each_block_b(F f) {
     run_block(f);
 }
 
@@ -391,7 +391,7 @@ void for_each_block_phased(int threads, size_t smem_bytes, uint32_t nphases,
             dim3((unsigned)threads), args, smem_bytes, stream()));
 }
 
-template <int MAXT = 0, class F>
+template <int MAXT = 0, int MINB = 1, class F>
 void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
                     const F& f) {
     if (!nblocks) return;
@@ -401,7 +401,7 @@ void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
     count_launch();
     void (*kern)(F);
     if constexpr (MAXT > 0) {
-        kern = k_for_each_block_b<F, MAXT>;
+        kern = k_for_each_block_b<F, MAXT, MINB>;
     } else {
         kern = k_for_each_block<F, MAXT>;
     }
