@@ -641,16 +641,16 @@ struct SpmvKernel {
 
 }  // namespace
 
-struct SparseLU::Impl {
+//! everything that depends on the sparsity pattern only: built once per
+//! topology, shared (read-only, host and device) by all solver instances --
+//! the ANM drivers create a new solver every iteration (libsanm/anm.cpp:205)
+struct LuTopo {
     std::shared_ptr<const Symbolic> sym;
     std::vector<uint32_t> h_rowptr, h_colidx;
-    rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list, rowperm, lperm;
+    rt::DBuf<uint32_t> rowptr, colidx, perm, structs, child_list;
     rt::DBuf<uint32_t> gptr, gsrc;
     rt::DBuf<int32_t> inv;
     rt::DBuf<uint64_t> a_dest;
-    rt::DBuf<double> fronts, vecs, vals, bp, xp, scal;
-    rt::DBuf<int> counters;
-    rt::DBuf<FrontD> fd;
     // per-level launch lists
     struct Level {
         uint32_t asm_off = 0, asm_n = 0;      //!< assembly tasks
@@ -665,14 +665,24 @@ struct SparseLU::Impl {
     rt::DBuf<LevelD> level_d;
     size_t solve_smem = 0;
     rt::DBuf<uint32_t> small_list, big_list;
+    uint32_t max_front = 0;
+};
+
+struct SparseLU::Impl {
+    std::shared_ptr<LuTopo> topo;
+    // numeric state of this instance
+    rt::DBuf<uint32_t> rowperm, lperm;
+    rt::DBuf<double> fronts, vecs, vals, bp, xp, scal;
+    rt::DBuf<int> counters;
+    rt::DBuf<FrontD> fd;
     bool factored = false;
 };
 
 SparseLU::SparseLU() : m_impl{new Impl} {}
 SparseLU::~SparseLU() = default;
 
-const uint32_t* SparseLU::d_rowptr() const { return m_impl->rowptr.ptr(); }
-const uint32_t* SparseLU::d_colidx() const { return m_impl->colidx.ptr(); }
+const uint32_t* SparseLU::d_rowptr() const { return m_impl->topo->rowptr.ptr(); }
+const uint32_t* SparseLU::d_colidx() const { return m_impl->topo->colidx.ptr(); }
 
 void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                        const uint32_t* colidx) {
@@ -681,31 +691,39 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     Impl& I = *m_impl;
     m_n = n;
     m_nnz = rowptr[n];
-    I.h_rowptr.assign(rowptr, rowptr + n + 1);
-    I.h_colidx.assign(colidx, colidx + m_nnz);
-    {
-        // the symbolic analysis depends on the pattern only: shared between
-        // solver instances (ANM iterations re-use one instance anyway; chained
-        // stages of a run create new ones)
-        static LruCache<const Symbolic> cache{6};
-        const uint64_t key = hash_vec(
-                I.h_colidx, hash_vec(I.h_rowptr, n * 0x51ED27ull + m_nnz));
-        I.sym = cache.get(key);
-        if (!I.sym || I.sym->n != n || I.sym->a_dest.size() != m_nnz) {
-            I.sym = std::make_shared<const Symbolic>(
-                    symbolic_analyze((uint32_t)n, rowptr, colidx));
-            cache.put(key, I.sym);
-        }
+    // Everything that depends on the pattern only (ordering, symbolic
+    // factorisation, launch lists, their device copies) is shared between
+    // solver instances: the ANM drivers build a new solver every iteration.
+    static LruCache<LuTopo> topo_cache{6};
+    const uint64_t key = hash_bytes(
+            colidx, m_nnz * sizeof(uint32_t),
+            hash_bytes(rowptr, (n + 1) * sizeof(uint32_t), n * 0x51ED27ull + m_nnz));
+    I.topo = topo_cache.get(key);
+    bool fresh = false;
+    if (!I.topo || I.topo->h_rowptr.size() != n + 1 ||
+        I.topo->h_colidx.size() != m_nnz ||
+        memcmp(I.topo->h_rowptr.data(), rowptr, (n + 1) * sizeof(uint32_t)) ||
+        memcmp(I.topo->h_colidx.data(), colidx, m_nnz * sizeof(uint32_t))) {
+        fresh = true;
+        I.topo = std::make_shared<LuTopo>();
+        I.topo->h_rowptr.assign(rowptr, rowptr + n + 1);
+        I.topo->h_colidx.assign(colidx, colidx + m_nnz);
+        I.topo->sym = std::make_shared<const Symbolic>(
+                symbolic_analyze((uint32_t)n, rowptr, colidx));
+        topo_cache.put(key, I.topo);
     }
-    const Symbolic& S = *I.sym;
+    LuTopo& T = *I.topo;
+    const Symbolic& S = *T.sym;
 
-    I.rowptr.upload(I.h_rowptr);
-    I.colidx.upload(I.h_colidx);
-    I.perm.upload(S.perm);
-    I.structs.upload(S.structs);
-    I.child_list.upload(S.child_list);
-    I.inv.upload(S.inv);
-    I.a_dest.upload(S.a_dest);
+    if (fresh) {
+        T.rowptr.upload(T.h_rowptr);
+        T.colidx.upload(T.h_colidx);
+        T.perm.upload(S.perm);
+        T.structs.upload(S.structs);
+        T.child_list.upload(S.child_list);
+        T.inv.upload(S.inv);
+        T.a_dest.upload(S.a_dest);
+    }
     I.fronts.alloc(S.front_total);
     I.vecs.alloc(S.soff[S.nsn]);
     I.rowperm.alloc(n);
@@ -720,7 +738,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     // flattened gather lists of the forward sweep: for row i of front s the
     // positions (in the work-vector array) of the children's update entries
     // that land on it, in child order
-    {
+    if (fresh) {
         std::vector<uint32_t> gptr(S.soff[S.nsn] + S.nsn + 1), gsrc;
         size_t at = 0;
         for (uint32_t s = 0; s < S.nsn; ++s) {
@@ -737,8 +755,8 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         }
         sanm_check(gsrc.size() < (1ull << 32) && S.soff[S.nsn] < (1ull << 32));
         if (gsrc.empty()) gsrc.push_back(0);
-        I.gptr.upload(gptr);
-        I.gsrc.upload(gsrc);
+        T.gptr.upload(gptr);
+        T.gsrc.upload(gsrc);
     }
 
     std::vector<FrontD> fd(S.nsn);
@@ -747,11 +765,11 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         FrontD& f = fd[s];
         f.F = I.fronts.ptr() + S.foff[s];
         f.vec = I.vecs.ptr() + S.soff[s];
-        f.st = I.structs.ptr() + S.soff[s];
-        f.inv = S.sn_parent[s] >= 0 ? I.inv.ptr() + S.inv_off[s] : nullptr;
+        f.st = T.structs.ptr() + S.soff[s];
+        f.inv = S.sn_parent[s] >= 0 ? T.inv.ptr() + S.inv_off[s] : nullptr;
         f.rowperm = I.rowperm.ptr() + S.sn_c0[s];
         f.lperm = I.lperm.ptr() + (size_t)s * NB;
-        f.gptr = I.gptr.ptr() + S.soff[s] + s;
+        f.gptr = T.gptr.ptr() + S.soff[s] + s;
         f.nr = S.sn_nr[s];
         f.nc = S.sn_nc[s];
         f.c0 = S.sn_c0[s];
@@ -766,11 +784,12 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.fd.upload(fd);
 
     const uint32_t nlev = (uint32_t)S.level_ptr.size() - 1;
-    I.levels.assign(nlev, {});
+    if (fresh) {
+    T.levels.assign(nlev, {});
     std::vector<Task> asm_t, fwd_t, bwd_t;
     std::vector<uint32_t> small_l, big_l;
     for (uint32_t l = 0; l < nlev; ++l) {
-        auto& L = I.levels[l];
+        auto& L = T.levels[l];
         L.asm_off = (uint32_t)asm_t.size();
         L.small_off = (uint32_t)small_l.size();
         L.big_off = (uint32_t)big_l.size();
@@ -810,7 +829,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         std::vector<LevelD> ld(nlev);
         size_t sm = 0;
         for (uint32_t l = 0; l < nlev; ++l) {
-            const auto& L = I.levels[l];
+            const auto& L = T.levels[l];
             const bool fw = L.max_nc >= SOLVE_WIDE_COLS, bw = L.max_nr >= SOLVE_WIDE_COLS;
             ld[l] = {L.fwd_off, L.fwd_n, L.bwd_off, L.bwd_n, fw, bw};
             sm = std::max(sm, 2 * (size_t)L.max_nc +
@@ -820,14 +839,15 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                                       (bw ? solve_scratch_doubles<BWD_ROWS, BWD_GROUPS_WIDE>()
                                           : solve_scratch_doubles<BWD_ROWS, BWD_GROUPS_NARROW>()));
         }
-        I.level_d.upload(ld);
-        I.solve_smem = sm * sizeof(double);
+        T.level_d.upload(ld);
+        T.solve_smem = sm * sizeof(double);
     }
-    I.asm_tasks.upload(asm_t);
-    I.fwd_tasks.upload(fwd_t);
-    I.bwd_tasks.upload(bwd_t);
-    I.small_list.upload(small_l);
-    I.big_list.upload(big_l);
+    T.asm_tasks.upload(asm_t);
+    T.fwd_tasks.upload(fwd_t);
+    T.bwd_tasks.upload(bwd_t);
+    T.small_list.upload(small_l);
+    T.big_list.upload(big_l);
+    }  // fresh
 
     if (getenv("SANM_LU_DEBUG")) {
         printf("[lu] n=%zu nnz=%zu nsn=%u levels=%u factor_entries=%zu "
@@ -845,8 +865,8 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
             }
             printf("[lu]  level %2u: fronts=%5u max_nc=%4u max_nr=%4u "
                    "entries=%9zu fwd_tasks=%u bwd_tasks=%u\n",
-                   l, cnt, mnc, mnr, (size_t)ent, I.levels[l].fwd_n,
-                   I.levels[l].bwd_n);
+                   l, cnt, mnc, mnr, (size_t)ent, T.levels[l].fwd_n,
+                   T.levels[l].bwd_n);
         }
         fflush(stdout);
     }
@@ -866,6 +886,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
 void SparseLU::factor(const double* vals_dev) {
     sanm_check(m_analyzed, "factor() before analyze()");
     Impl& I = *m_impl;
+    LuTopo& T = *I.topo;
     if (vals_dev != I.vals.ptr()) {
         rt::d2d(I.vals.ptr(), vals_dev, m_nnz * sizeof(double));
     }
@@ -878,26 +899,26 @@ void SparseLU::factor(const double* vals_dev) {
     rt::for_each_block<256>(1, 256, 256 * sizeof(double),
                        AbsMaxKernel{I.scal.ptr() + 4, ABSMAX_BLOCKS, 1,
                                     I.scal.ptr()});
-    rt::for_each(m_nnz, ScatterA{I.fronts.ptr(), I.a_dest.ptr(), I.vals.ptr()});
+    rt::for_each(m_nnz, ScatterA{I.fronts.ptr(), T.a_dest.ptr(), I.vals.ptr()});
     const double* amax = I.scal.ptr();
     int* npert = I.counters.ptr();
-    for (auto& L : I.levels) {
+    for (auto& L : T.levels) {
         if (L.asm_n) {
             LuScope ps{"lu_asm"};
             rt::for_each_block<256>(L.asm_n, 256, 0,
-                               AssembleChildren{I.fd.ptr(), I.child_list.ptr(),
-                                                I.asm_tasks.ptr() + L.asm_off});
+                               AssembleChildren{I.fd.ptr(), T.child_list.ptr(),
+                                                T.asm_tasks.ptr() + L.asm_off});
         }
         if (L.small_n) {
             size_t smem = (size_t)L.small_max_nr * L.small_max_nr * sizeof(double) + 16;
             LuScope ps{"lu_small"};
             rt::for_each_block<256>(L.small_n, 256, smem,
                                SmallFrontKernel{I.fd.ptr(),
-                                                I.small_list.ptr() + L.small_off,
+                                                T.small_list.ptr() + L.small_off,
                                                 amax, npert});
         }
         if (L.big_n) {
-            const uint32_t* list = I.big_list.ptr() + L.big_off;
+            const uint32_t* list = T.big_list.ptr() + L.big_off;
             const uint32_t tiles = (L.big_max_nr + 63) / 64;
             for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
                 {
@@ -934,22 +955,23 @@ void SparseLU::factor(const double* vals_dev) {
 
 void SparseLU::solve(double* x_dev, const double* b_dev) {
     Impl& I = *m_impl;
+    LuTopo& T = *I.topo;
     sanm_check(I.factored, "solve() before factor()");
     // b may alias x: the forward sweep has consumed b before the backward
     // sweep writes x
     static const bool per_level = getenv("SANM_LU_PER_LEVEL") != nullptr;
     if (!per_level && !g_lu_prof && m_n <= 12000) {
-        const uint32_t nlev = (uint32_t)I.levels.size();
+        const uint32_t nlev = (uint32_t)T.levels.size();
         rt::for_each_block_phased<512>(
-                512, I.solve_smem, 2 * nlev,
-                SolvePhased{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
-                            I.fwd_tasks.ptr(), I.bwd_tasks.ptr(), I.level_d.ptr(),
-                            nlev, b_dev, I.perm.ptr(), I.xp.ptr(), x_dev});
+                512, T.solve_smem, 2 * nlev,
+                SolvePhased{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                            T.fwd_tasks.ptr(), T.bwd_tasks.ptr(), T.level_d.ptr(),
+                            nlev, b_dev, T.perm.ptr(), I.xp.ptr(), x_dev});
         return;
     }
     char tag[32];
-    for (auto& L : I.levels) {
-        snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - I.levels.data()));
+    for (auto& L : T.levels) {
+        snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - T.levels.data()));
         LuScope ps{tag};
         constexpr int R = FWD_ROWS;
         if (L.max_nc >= SOLVE_WIDE_COLS) {
@@ -957,21 +979,21 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
             rt::for_each_block<R * G>(
                     L.fwd_n, R * G,
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
-                    ForwardKernel<R, G>{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
-                                     I.fwd_tasks.ptr() + L.fwd_off, b_dev,
-                                     I.perm.ptr()});
+                    ForwardKernel<R, G>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                                     T.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                     T.perm.ptr()});
         } else {
             constexpr int G = FWD_GROUPS_NARROW;
             rt::for_each_block<R * G>(
                     L.fwd_n, R * G,
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
-                    ForwardKernel<R, G>{I.fd.ptr(), I.gsrc.ptr(), I.vecs.ptr(),
-                                     I.fwd_tasks.ptr() + L.fwd_off, b_dev,
-                                     I.perm.ptr()});
+                    ForwardKernel<R, G>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                                     T.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                     T.perm.ptr()});
         }
     }
-    for (size_t l = I.levels.size(); l-- > 0;) {
-        auto& L = I.levels[l];
+    for (size_t l = T.levels.size(); l-- > 0;) {
+        auto& L = T.levels[l];
         snprintf(tag, sizeof(tag), "lu_bwd_%02d", (int)l);
         LuScope ps{tag};
         constexpr int R = BWD_ROWS;
@@ -980,22 +1002,23 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
             rt::for_each_block<R * G>(
                     L.bwd_n, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
-                    BackwardKernel<R, G>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
-                                      I.xp.ptr(), x_dev, I.perm.ptr()});
+                    BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
+                                      I.xp.ptr(), x_dev, T.perm.ptr()});
         } else {
             constexpr int G = BWD_GROUPS_NARROW;
             rt::for_each_block<R * G>(
                     L.bwd_n, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
-                    BackwardKernel<R, G>{I.fd.ptr(), I.bwd_tasks.ptr() + L.bwd_off,
-                                      I.xp.ptr(), x_dev, I.perm.ptr()});
+                    BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
+                                      I.xp.ptr(), x_dev, T.perm.ptr()});
         }
     }
 }
 
 void SparseLU::apply(double* y_dev, const double* x_dev) const {
     const Impl& I = *m_impl;
-    rt::for_each(m_n, SpmvKernel{I.rowptr.ptr(), I.colidx.ptr(), I.vals.ptr(),
+    const LuTopo& T = *I.topo;
+    rt::for_each(m_n, SpmvKernel{T.rowptr.ptr(), T.colidx.ptr(), I.vals.ptr(),
                                  x_dev, y_dev});
 }
 
