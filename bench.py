@@ -120,30 +120,42 @@ class ClockSampler(threading.Thread):
         self.index = index
         self.samples = []
         self._stop_evt = threading.Event()
+        self._init_nvml()
 
-    def _run_nvml(self) -> bool:
-        """NVML directly (5 ms period): nvidia-smi takes ~100 ms per call, longer
-        than a short timed region"""
+    def _init_nvml(self):
+        """called from __init__: loading NVML takes ~100 ms, longer than a short
+        timed region"""
+        self._nv = None
         try:
             import pynvml as nv
             nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons",
-                                  None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
-            bits = [(0x08, "hw_slowdown"), (0x40, "hw_thermal_slowdown"),
-                    (0x20, "sw_thermal_slowdown"), (0x04, "sw_power_cap")]
+            self._h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self._mx = nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM)
+            self._reasons = getattr(
+                nv, "nvmlDeviceGetCurrentClocksEventReasons",
+                None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            self._nv = nv
         except Exception:
+            self._nv = None
+
+    def _sample_nvml(self):
+        bits = [(0x08, "hw_slowdown"), (0x40, "hw_thermal_slowdown"),
+                (0x20, "sw_thermal_slowdown"), (0x04, "sw_power_cap")]
+        try:
+            mhz = self._nv.nvmlDeviceGetClockInfo(self._h, self._nv.NVML_CLOCK_SM)
+            r = int(self._reasons(self._h))
+            self.samples.append(
+                [str(mhz), str(self._mx), "0"] +
+                ["Active" if r & bit else "Not Active" for bit, _ in bits])
+        except Exception:
+            pass
+
+    def _run_nvml(self) -> bool:
+        """NVML directly (5 ms period): nvidia-smi takes ~100 ms per call"""
+        if self._nv is None:
             return False
         while not self._stop_evt.is_set():
-            try:
-                mhz = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
-                r = int(get_reasons(h))
-                self.samples.append(
-                    [str(mhz), str(mx), "0"] +
-                    ["Active" if r & bit else "Not Active" for bit, _ in bits])
-            except Exception:
-                pass
+            self._sample_nvml()
             self._stop_evt.wait(0.005)
         return True
 

@@ -345,11 +345,12 @@ void FusedProp::launch_step(int k_push, int kb, bool want_out, const double* x) 
         }
     } else {
         SANM_PROF("k_fused_step");
-        // unbounded launch on purpose: with __launch_bounds__(128, 1) ptxas takes
-        // 255 registers (2.42 -> 1.76 G tet*order/s), with (128, 3) it trades
-        // ILP for occupancy (2.24 G); its own choice of 166-240 is the best
+        // occupancy target per energy model (fused_dev.h M::MINB, measured):
+        // the kernel is HBM-bound and wants as many loads in flight as the
+        // register file allows; __launch_bounds__(128, 1) (255 registers) gives
+        // 1.76 G tet*order/s where (128, 5) gives 2.49 G
         if (use_io) {
-            rt::for_each_block(
+            rt::for_each_block<TILE, M::MINB>(
                     ntiles, TILE, smem,
                     StepKernel<M, true>{a, io, k_push, kb, (int)want_out});
         } else {

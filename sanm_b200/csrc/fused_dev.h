@@ -110,6 +110,11 @@ SANM_HD inline void neg_gfg(double* R, const double* G0, const double* Fk) {
  */
 struct NHC {
     static constexpr int S = 19;
+    //! resident 128-thread blocks per SM the order-step kernel is compiled for
+    //! (__launch_bounds__(128, MINB)); measured on B200, 2 M tets, K = 20:
+    //! unbounded (ptxas picks 128 regs = 4 blocks) 2.43 G tet*order/s, 4: 2.43,
+    //! 5: 2.49, 6: 2.33 (spills)
+    static constexpr int MINB = 5;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18 };
     struct Acc {
@@ -190,6 +195,8 @@ struct NHC {
  */
 struct NHI {
     static constexpr int S = 23;
+    //! unbounded (236 regs = 2 blocks) 1.61 G, 4: 1.85, 5: 1.61
+    static constexpr int MINB = 4;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18, oJ = 19, oQ = 20, oI = 21, oT = 22 };
     struct Acc {
@@ -307,6 +314,8 @@ struct NHI {
  */
 struct ARAP {
     static constexpr int S = 27;
+    //! unbounded (240 regs = 2 blocks) 1.43 G, 4: 1.56, 5: 1.55
+    static constexpr int MINB = 4;
     static constexpr int AUX = 12;
     enum { oF = 0, oP = 9, oW = 18 };
     struct Acc {

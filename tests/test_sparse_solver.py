@@ -76,7 +76,12 @@ def test_zero_diagonal_small(impl):
 
 
 @pytest.mark.parametrize("shape,nonsym", [((5, 4, 3), 0.0), ((9, 8, 7), 0.3),
-                                          ((16, 12, 10), 0.0)])
+                                          ((16, 12, 10), 0.0),
+                                          # 13,824 unknowns: above the size
+                                          # where the solve switches from the
+                                          # one persistent launch to one
+                                          # launch per level
+                                          ((24, 16, 12), 0.2)])
 def test_grid_blocks(impl, shape, nonsym):
     rng = np.random.default_rng(11)
     A = grid_matrix(*shape, rng, nonsym=nonsym)
