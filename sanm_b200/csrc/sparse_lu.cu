@@ -315,13 +315,27 @@ struct BigRowPanelKernel {
             R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + f.lperm[i]];
         }
         c.sync();
-        for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
-            uint32_t i = e % nb, j = e / nb;
-            uint32_t gj = j0 + j;
-            if (gj >= kb && gj < kb + nb) continue;
-            double s = 0;
-            for (uint32_t m = 0; m < nb; ++m) s += Di[m * NB + i] * R[j * NB + m];
-            f.F[(uint64_t)gj * f.nr + kb + i] = s;
+        // 4 rows x 2 columns per thread (8 x 32 thread grid in the CUDA build):
+        // 8 FMAs per 6 shared loads instead of 1 per 2 -- the plain dot-product
+        // form is bound by shared-memory bandwidth.  Entries past nb / nj are
+        // computed from stale shared memory and never stored.
+        for (uint32_t q = c.tid; q < 256; q += c.nthr) {
+            const uint32_t i4 = (q % 8) * 4, j2 = (q / 8) * 2;
+            double acc[4][2] = {};
+            for (uint32_t m = 0; m < nb; ++m) {
+                double a[4], b[2];
+                for (int u = 0; u < 4; ++u) a[u] = Di[m * NB + i4 + u];
+                for (int v = 0; v < 2; ++v) b[v] = R[(j2 + v) * NB + m];
+                for (int u = 0; u < 4; ++u)
+                    for (int v = 0; v < 2; ++v) acc[u][v] += a[u] * b[v];
+            }
+            for (int v = 0; v < 2; ++v) {
+                const uint32_t gj = j0 + j2 + v;
+                if (j2 + v >= nj || (gj >= kb && gj < kb + nb)) continue;
+                for (int u = 0; u < 4; ++u) {
+                    if (i4 + u < nb) f.F[(uint64_t)gj * f.nr + kb + i4 + u] = acc[u][v];
+                }
+            }
         }
     }
 };
@@ -399,13 +413,25 @@ struct BigColPanelKernel {
             Cs[m * 64 + i] = f.F[(uint64_t)(kb + m) * f.nr + i0 + i];
         }
         c.sync();
-        for (uint32_t e = c.tid; e < nb * ni; e += c.nthr) {
-            uint32_t i = e % ni, q = e / ni;
-            uint32_t gi = i0 + i;
-            if (gi >= kb && gi < kb + nb) continue;
-            double s = 0;
-            for (uint32_t m = 0; m < nb; ++m) s += Cs[m * 64 + i] * Di[q * NB + m];
-            f.F[(uint64_t)(kb + q) * f.nr + gi] = -s;
+        // 4 rows x 2 columns per thread (16 x 16 thread grid), see the row panel
+        for (uint32_t t = c.tid; t < 256; t += c.nthr) {
+            const uint32_t i4 = (t % 16) * 4, q2 = (t / 16) * 2;
+            double acc[4][2] = {};
+            for (uint32_t m = 0; m < nb; ++m) {
+                double a[4], b[2];
+                for (int u = 0; u < 4; ++u) a[u] = Cs[m * 64 + i4 + u];
+                for (int v = 0; v < 2; ++v) b[v] = Di[(q2 + v) * NB + m];
+                for (int u = 0; u < 4; ++u)
+                    for (int v = 0; v < 2; ++v) acc[u][v] += a[u] * b[v];
+            }
+            for (int v = 0; v < 2; ++v) {
+                if (q2 + v >= nb) continue;
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t gi = i0 + i4 + u;
+                    if (i4 + u >= ni || (gi >= kb && gi < kb + nb)) continue;
+                    f.F[(uint64_t)(kb + q2 + v) * f.nr + gi] = -acc[u][v];
+                }
+            }
         }
     }
 };
