@@ -183,6 +183,13 @@ int sanm_sweep_run(sanm_sweep_t* s);
  * soon as order k has been assembled (two copy streams beside the compute
  * stream); returns when b has arrived.  Same results as the three calls. */
 int sanm_sweep_run_host(sanm_sweep_t* s, const double* x, double* b);
+/* asynchronous form of run_host: submit enqueues one sweep and returns;
+ * consecutive submissions alternate between two sets of device buffers, so the
+ * uploads / downloads of one sweep overlap the kernels of the other.  x must
+ * stay valid until its sweep has started, b until sanm_sweep_wait_host(),
+ * which returns when every submitted sweep has delivered its b. */
+int sanm_sweep_submit_host(sanm_sweep_t* s, const double* x, double* b);
+int sanm_sweep_wait_host(sanm_sweep_t* s);
 /* Multi-rank exchange of the assembled right-hand sides.  mode 0 (default):
  * all-reduce of the full vectors, every rank ends with all of b (what the
  * replicated solver of the ANM drivers needs).  mode 1: nodal vectors stay

@@ -630,6 +630,17 @@ class ElementSweep:
         self.b.call("sweep_get_b", self.h, _ptr(out))
         return out
 
+    def submit_host(self, x, out):
+        """asynchronous run_host; keep x and out alive until wait_host()"""
+        assert x.dtype == np.float64 and x.flags.c_contiguous
+        assert x.shape == (self.order + 1, self.n_in)
+        assert out.dtype == np.float64 and out.flags.c_contiguous
+        assert out.shape == (self.order + 1, self.n_out)
+        self.b.call("sweep_submit_host", self.h, _ptr(x), _ptr(out))
+
+    def wait_host(self):
+        self.b.call("sweep_wait_host", self.h)
+
     def set_exchange(self, mode: int):
         """0: all-reduce of full vectors; 1: distributed vectors, halo sums"""
         self.b.call("sweep_set_exchange", self.h, C.c_int(mode))

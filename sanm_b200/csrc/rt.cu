@@ -50,6 +50,7 @@ void* fence_pipe(int) { return nullptr; }
 void main_wait(void*) {}
 void pipe_wait(int, void*) {}
 void pipe_sync(int) {}
+void fence_drop(void*) {}
 void* hmalloc_pinned(size_t bytes) { return malloc(bytes ? bytes : 1); }
 void hfree_pinned(void* p) { free(p); }
 
@@ -187,6 +188,9 @@ void* fence_pipe(int pipe) { return fence_on(pipe_stream(pipe)); }
 void main_wait(void* fence) { wait_on(stream(), fence); }
 void pipe_wait(int pipe, void* fence) { wait_on(pipe_stream(pipe), fence); }
 void pipe_sync(int pipe) { SANM_CUDA_CHECK(cudaStreamSynchronize(pipe_stream(pipe))); }
+void fence_drop(void* fence) {
+    if (fence) cudaEventDestroy(static_cast<cudaEvent_t>(fence));
+}
 
 void* hmalloc_pinned(size_t bytes) {
     check_device();

@@ -169,6 +169,7 @@ void* fence_pipe(int pipe);
 void main_wait(void* fence);           //!< main stream waits; consumes the fence
 void pipe_wait(int pipe, void* fence); //!< pipe waits; consumes the fence
 void pipe_sync(int pipe);              //!< host waits for the pipe
+void fence_drop(void* fence);          //!< release a fence nobody waited for
 //! pinned host staging memory (plain malloc in the host build)
 void* hmalloc_pinned(size_t bytes);
 void hfree_pinned(void* p);

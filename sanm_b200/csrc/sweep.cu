@@ -20,8 +20,9 @@ public:
         m_prop.reset(new TaylorProp{std::move(g), f, order});
         m_nin = m_rin->nr_in();
         m_nout = m_rout->nr_out();
-        m_x.alloc((size_t)(order + 1) * m_nin);
-        m_b.alloc((size_t)(order + 1) * m_nout);
+        m_xbuf[0].alloc((size_t)(order + 1) * m_nin);
+        m_bbuf[0].alloc((size_t)(order + 1) * m_nout);
+        use_buffer(0);
         m_prop->prepare(m_rin->out_shape());
         sanm_check(m_rout->nr_in() == m_prop->batch() * m_prop->out_elems(),
                    "remap_out input size does not match the function output");
@@ -65,7 +66,8 @@ public:
     }
 
     void set_x(const double* x) {
-        rt::h2d(m_x.ptr(), x, m_x.size() * sizeof(double));
+        use_buffer(0);
+        rt::h2d(m_xp, x, m_xbuf[0].size() * sizeof(double));
     }
 
     void run() {
@@ -78,15 +80,42 @@ public:
      * device->host pipe as soon as order k has been assembled.  Returns when
      * b has arrived.  x and b should be pinned for the copies to overlap. */
     void run_host(const double* x, double* b) {
+        submit_host(x, b);
+        wait_host();
+    }
+
+    /*! Asynchronous form: enqueue one sweep (uploads, kernels, downloads) and
+     * return.  Consecutive submissions alternate between two sets of device
+     * buffers, so the uploads of sweep s+1 and the downloads of sweep s overlap
+     * the kernels of the other (the kernels themselves run one sweep after the
+     * other: there is one Taylor state).  x must stay valid until its sweep has
+     * started, b until wait_host(). */
+    void submit_host(const double* x, double* b) {
         const int K = m_order;
-        // kernels of an earlier sweep may still be reading m_x
-        rt::pipe_wait(rt::PIPE_H2D, rt::fence_main());
+        const int idx = (int)(m_submitted++ & 1);
+        if (!m_xbuf[idx].size()) {
+            m_xbuf[idx].alloc((size_t)(K + 1) * m_nin);
+            m_bbuf[idx].alloc((size_t)(K + 1) * m_nout);
+        }
+        use_buffer(idx);
+        // the sweep that used these buffers before must have read its x ...
+        if (m_kernels_done[idx]) {
+            rt::pipe_wait(rt::PIPE_H2D, m_kernels_done[idx]);
+            m_kernels_done[idx] = nullptr;
+        } else {
+            rt::pipe_wait(rt::PIPE_H2D, rt::fence_main());
+        }
+        // ... and its b must have left before the new kernels overwrite it
+        if (m_d2h_done[idx]) {
+            rt::main_wait(m_d2h_done[idx]);
+            m_d2h_done[idx] = nullptr;
+        }
         std::vector<void*> arrived(K + 1, nullptr);
         // distributed mode: only what the local tets read / contribute to
         const uint64_t xlo = m_halo_mode ? m_x_lo : 0, xhi = m_halo_mode ? m_x_hi : m_nin;
         const uint64_t blo = m_halo_mode ? m_b_lo : 0, bhi = m_halo_mode ? m_b_hi : m_nout;
         for (int k = 0; k <= K; ++k) {
-            rt::pipe_h2d(m_x.ptr() + (size_t)k * m_nin + xlo,
+            rt::pipe_h2d(m_xp + (size_t)k * m_nin + xlo,
                          x + (size_t)k * m_nin + xlo, (xhi - xlo) * sizeof(double));
             // x_K is never pushed (libsanm/anm.cpp:205-290: the last order
             // only produces its bias), but it is part of the caller's series
@@ -100,7 +129,7 @@ public:
                 [&](int k) {
                     rt::pipe_wait(rt::PIPE_D2H, rt::fence_main());
                     rt::pipe_d2h(b + (size_t)k * m_nout + blo,
-                                 m_b.ptr() + (size_t)k * m_nout + blo,
+                                 m_bp + (size_t)k * m_nout + blo,
                                  (bhi - blo) * sizeof(double));
                 });
         // x_K: nothing on the main stream waits for it; keep stream order sane
@@ -110,9 +139,20 @@ public:
                 f = nullptr;
             }
         }
+        m_kernels_done[idx] = rt::fence_main();
+        m_d2h_done[idx] = rt::fence_pipe(rt::PIPE_D2H);
+    }
+
+    //! all submitted sweeps have finished and their b have arrived
+    void wait_host() {
         rt::pipe_sync(rt::PIPE_D2H);
         rt::sync();
         m_prop->check_device_error();
+    }
+
+    ~ElementSweep() {
+        for (void*& f : m_kernels_done) rt::fence_drop(f);
+        for (void*& f : m_d2h_done) rt::fence_drop(f);
     }
 
 private:
@@ -135,24 +175,24 @@ private:
             {
                 SANM_PROF("push_xi");
                 before_x(0);
-                p.push_xi_from(m_x.ptr(), m_b.ptr());
-                exchange(m_b.ptr());
+                p.push_xi_from(m_xp, m_bp);
+                exchange(m_bp);
                 after_b(0);
             }
             for (int k = 1; k <= K; ++k) {
                 {
                     SANM_PROF("taylor_next_order");
-                    p.compute_next_order_bias_to(m_b.ptr() + (size_t)k * m_nout);
+                    p.compute_next_order_bias_to(m_bp + (size_t)k * m_nout);
                     // the reference computes the per-tet Jacobian inside its
                     // first compute_next_order_bias (libsanm/symbolic.cpp:249-252)
                     if (k == 1) p.ensure_jacobian();
-                    exchange(m_b.ptr() + (size_t)k * m_nout);
+                    exchange(m_bp + (size_t)k * m_nout);
                     after_b(k);
                 }
                 if (k < K) {
                     SANM_PROF("push_xi");
                     before_x(k);
-                    p.push_xi_from(m_x.ptr() + (size_t)k * m_nin);
+                    p.push_xi_from(m_xp + (size_t)k * m_nin);
                 }
             }
             return;
@@ -162,13 +202,13 @@ private:
         {
             SANM_PROF("push_xi");
             before_x(0);
-            m_rin->apply(p.input_slot(0), soa_in, m_x.ptr(), VecLayout{});
+            m_rin->apply(p.input_slot(0), soa_in, m_xp, VecLayout{});
             p.push_xi_filled();
         }
         {
             SANM_PROF("remap_out");
-            m_rout->apply(m_b.ptr(), VecLayout{}, p.output_slot(0), soa_out);
-            exchange(m_b.ptr());
+            m_rout->apply(m_bp, VecLayout{}, p.output_slot(0), soa_out);
+            exchange(m_bp);
             after_b(0);
         }
         for (int k = 1; k <= K; ++k) {
@@ -178,16 +218,16 @@ private:
             }
             {
                 SANM_PROF("remap_out");
-                m_rout->apply(m_b.ptr() + (size_t)k * m_nout, VecLayout{},
+                m_rout->apply(m_bp + (size_t)k * m_nout, VecLayout{},
                               p.output_slot(k), soa_out);
-                exchange(m_b.ptr() + (size_t)k * m_nout);
+                exchange(m_bp + (size_t)k * m_nout);
                 after_b(k);
             }
             if (k < K) {
                 SANM_PROF("push_xi");
                 before_x(k);
                 m_rin->apply(p.input_slot(k), soa_in,
-                             m_x.ptr() + (size_t)k * m_nin, VecLayout{});
+                             m_xp + (size_t)k * m_nin, VecLayout{});
                 p.push_xi_filled();
             }
         }
@@ -195,7 +235,7 @@ private:
 
 public:
     void get_b(double* b) {
-        rt::d2h(b, m_b.ptr(), m_b.size() * sizeof(double));
+        rt::d2h(b, m_bp, m_bbuf[0].size() * sizeof(double));
         m_prop->check_device_error();
     }
 
@@ -222,7 +262,18 @@ private:
     bool m_halo_mode = false;
     comm::Halo m_halo;
     std::unique_ptr<TaylorProp> m_prop;
-    rt::DBuf<double> m_x, m_b;
+    //! two sets of device series: consecutive submit_host() calls alternate, so
+    //! the transfers of one sweep overlap the kernels of the other
+    rt::DBuf<double> m_xbuf[2], m_bbuf[2];
+    double* m_xp = nullptr;  //!< buffers of the sweep being enqueued
+    double* m_bp = nullptr;
+    uint64_t m_submitted = 0;
+    void* m_kernels_done[2] = {nullptr, nullptr};  //!< fence: sweep read x / wrote b
+    void* m_d2h_done[2] = {nullptr, nullptr};      //!< fence: b left the device
+    void use_buffer(int i) {
+        m_xp = m_xbuf[i].ptr();
+        m_bp = m_bbuf[i].ptr();
+    }
 };
 
 }  // namespace sanm_b200
@@ -254,6 +305,12 @@ int sanm_sweep_run(sanm_sweep_t* s) {
 }
 int sanm_sweep_run_host(sanm_sweep_t* s, const double* x, double* b) {
     return capi::guard([&] { s->s->run_host(x, b); });
+}
+int sanm_sweep_submit_host(sanm_sweep_t* s, const double* x, double* b) {
+    return capi::guard([&] { s->s->submit_host(x, b); });
+}
+int sanm_sweep_wait_host(sanm_sweep_t* s) {
+    return capi::guard([&] { s->s->wait_host(); });
 }
 int sanm_sweep_set_exchange(sanm_sweep_t* s, int mode) {
     return capi::guard([&] { s->s->set_exchange(mode); });

@@ -76,6 +76,13 @@ def check_sweep(impl, ref, dims, energy, order, **kw):
     # call overwrites x while kernels of the first may still be queued)
     for _ in range(2):
         assert np.array_equal(got, sw.run_host(x))
+    # asynchronous form: three sweeps in flight over the two buffer sets
+    outs = [np.zeros_like(got) for _ in range(3)]
+    for o in outs:
+        sw.submit_host(x, o)
+    sw.wait_host()
+    for o in outs:
+        assert np.array_equal(got, o)
     want = reference_sweep(rmodel.y, rmodel.lt_inp.desc, rmodel.lt_out, x)
     for k in range(order + 1):
         scale = max(np.abs(want[k]).max(), 1e-300)
