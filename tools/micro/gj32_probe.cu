@@ -1,4 +1,5 @@
 // Micro-probe (tools only; not part of the library): 32x32 Gauss-Jordan with
+// build: nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o gj32_probe gj32_probe.cu
 // partial pivoting by 4 warps, each owning 8 columns; checks inv(P A) and
 // prints the cycles per phase.
 #include <cstdio>
