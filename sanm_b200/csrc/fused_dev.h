@@ -33,6 +33,9 @@
  * contiguous S*TILE*8-byte block.
  */
 #pragma once
+#ifndef SANM_STREAMING_SLOTS
+#define SANM_STREAMING_SLOTS 1
+#endif
 
 #include "taylor_dev.h"
 
@@ -56,12 +59,24 @@ using taylor::inv3;
 template <int N>
 SANM_HD inline void ld_strided(double* dst, const double* p) {
 #pragma unroll
-    for (int c = 0; c < N; ++c) dst[c] = p[c * TILE];
+    for (int c = 0; c < N; ++c) {
+#if defined(__CUDA_ARCH__) && SANM_STREAMING_SLOTS
+        dst[c] = __ldcs(p + c * TILE);  // read once per launch: evict first
+#else
+        dst[c] = p[c * TILE];
+#endif
+    }
 }
 template <int N>
 SANM_HD inline void st_strided(double* p, const double* src) {
 #pragma unroll
-    for (int c = 0; c < N; ++c) p[c * TILE] = src[c];
+    for (int c = 0; c < N; ++c) {
+#if defined(__CUDA_ARCH__) && SANM_STREAMING_SLOTS
+        __stcs(p + c * TILE, src[c]);
+#else
+        p[c * TILE] = src[c];
+#endif
+    }
 }
 
 //! C += s * A B (3x3 row-major)
