@@ -436,6 +436,32 @@ struct BigColPanelKernel {
     }
 };
 
+/*! Column panel of step kb and pivot block of step kb + NB in ONE launch.
+ * The two are independent: the column panel reads the inverted block kb and
+ * writes columns kb .. kb+NB outside it, the next pivot block lies in columns
+ * kb+NB ..  and was finished by the GEMM of step kb.  The pivot block is a
+ * single 128-thread block per front on the critical path (~10 us of dependent
+ * shared-memory round trips); run beside the column panel it costs no launch
+ * of its own.  Blocks [0, nfronts) are the pivot blocks (scheduled first),
+ * the rest the panel tiles. */
+struct BigColDiagKernel {
+    BigColPanelKernel col;
+    BigDiagKernel diag;
+    uint32_t nfronts;
+    SANM_D void operator()(const rt::BlockCtx& c) const {
+        rt::BlockCtx c2 = c;
+        if (c.bid < nfronts) {
+            // gj32.cuh wants exactly 4 warps; warps 4..7 leave as a whole
+            if (c.tid >= 128) return;
+            if (c2.nthr > 128) c2.nthr = 128;
+            diag(c2);
+        } else {
+            c2.bid = c.bid - nfronts;
+            col(c2);
+        }
+    }
+};
+
 /* ---- solves */
 
 /* Solve kernels.  A task is one chunk of ROWS rows of one front; a block of
@@ -946,19 +972,19 @@ void SparseLU::factor(const double* vals_dev) {
         if (L.big_n) {
             const uint32_t* list = T.big_list.ptr() + L.big_off;
             const uint32_t tiles = (L.big_max_nr + 63) / 64;
+            const size_t diag_smem =
+                    (NB * NB + 2 * NB) * sizeof(double) + NB * sizeof(uint32_t) + 16;
+            const size_t panel_smem = (NB * NB + NB * 64) * sizeof(double);
+            {
+                LuScope ps{"lu_diag"};
+                // 4 warps per front (gj32.cuh)
+                rt::for_each_block<128>(L.big_n, 128, diag_smem,
+                                        BigDiagKernel{I.fd.ptr(), list, 0, amax, npert});
+            }
             for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
                 {
-                    LuScope ps{"lu_diag"};
-                    // 4 warps per front (gj32.cuh)
-                    rt::for_each_block<128>(
-                            L.big_n, 128,
-                            (NB * NB + 2 * NB) * sizeof(double) + NB * sizeof(uint32_t) + 16,
-                            BigDiagKernel{I.fd.ptr(), list, kb, amax, npert});
-                }
-                {
                     LuScope ps{"lu_row"};
-                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256,
-                                       (NB * NB + NB * 64) * sizeof(double),
+                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256, panel_smem,
                                        BigRowPanelKernel{I.fd.ptr(), list, kb, tiles});
                 }
                 {
@@ -967,11 +993,20 @@ void SparseLU::factor(const double* vals_dev) {
                                        2 * NB * 64 * sizeof(double),
                                        BigGemmKernel{I.fd.ptr(), list, kb, tiles});
                 }
-                {
+                BigColPanelKernel col{I.fd.ptr(), list, kb, tiles};
+                if (kb + NB < L.big_max_nc) {
+                    // column panel of this step beside the pivot block of the next
+                    LuScope ps{"lu_col_diag"};
+                    rt::for_each_block<256>(
+                            (size_t)L.big_n * (tiles + 1), 256,
+                            std::max(diag_smem, panel_smem),
+                            BigColDiagKernel{col,
+                                             BigDiagKernel{I.fd.ptr(), list, kb + NB, amax,
+                                                           npert},
+                                             L.big_n});
+                } else {
                     LuScope ps{"lu_col"};
-                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256,
-                                       (NB * NB + NB * 64) * sizeof(double),
-                                       BigColPanelKernel{I.fd.ptr(), list, kb, tiles});
+                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256, panel_smem, col);
                 }
             }
         }
