@@ -38,7 +38,7 @@ struct FrontD {
     const uint32_t* st;  //!< row structure (permuted indices)
     const int32_t* inv;  //!< map parent row -> own update row (size nr_parent)
     uint32_t* rowperm;   //!< [nc] row permutation of the pivot block
-    uint32_t* lperm;     //!< [NB] row permutation of the current pivot step
+    uint32_t* lperm;     //!< [2][NB] row permutation of the pivot step, by step parity
     const uint32_t* gptr;  //!< [nr + 1] child contributions of row i: gsrc[gptr[i] .. gptr[i+1])
     uint32_t nr, nc, c0;
     uint32_t child_begin, child_end;
@@ -283,7 +283,8 @@ struct BigDiagKernel {
 #endif
         // row i of the block now holds original row lperm[i]; the rest of
         // the block row is permuted by BigRowPanelKernel while it loads it
-        for (uint32_t i = c.tid; i < nb; i += c.nthr) f.lperm[i] = lperm[i];
+        // by step parity: the row panel of step kb - NB may still be reading its own
+        for (uint32_t i = c.tid; i < nb; i += c.nthr) f.lperm[((kb / NB) & 1) * NB + i] = lperm[i];
         c.sync();
         // pivoting never leaves the block: position kb + i of the front holds
         // the original row kb + lperm[i]
@@ -310,9 +311,10 @@ struct BigRowPanelKernel {
             Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
         }
         // rows of the pivot block were swapped by BigDiagKernel (lperm)
+        const uint32_t* lp = f.lperm + ((kb / NB) & 1) * NB;
         for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
             uint32_t i = e % nb, j = e / nb;
-            R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + f.lperm[i]];
+            R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + lp[i]];
         }
         c.sync();
         // 4 rows x 2 columns per thread (8 x 32 thread grid in the CUDA build):
@@ -340,7 +342,11 @@ struct BigRowPanelKernel {
     }
 };
 
-//! T -= C * R' on a 64x64 tile (rows and columns of the pivot block excluded)
+/*! T -= C * R' on a 64x64 tile (rows and columns of the pivot block excluded).
+ * R' = Dinv * R is recomputed per tile from the untouched block row (a third
+ * of the tile's flops, in a latency-bound kernel) instead of being read back
+ * from a row-panel launch before it: BigRowPanelKernel stores R' in the launch
+ * AFTER this one, beside the column panel and the next pivot block. */
 struct BigGemmKernel {
     const FrontD* fronts;
     const uint32_t* list;
@@ -353,6 +359,9 @@ struct BigGemmKernel {
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
         double* Cs = reinterpret_cast<double*>(c.smem);  // [NB][64] : Cs[m*64+i]
         double* Rs = Cs + NB * 64;                       // [64][NB] : Rs[j*NB+m]
+        double* Rr = Rs + NB * 64;                       // [64][NB] : R before Dinv
+        double* Di = Rr + NB * 64;                       // [NB*NB]
+        const uint32_t* lp = f.lperm + ((kb / NB) & 1) * NB;
         const uint32_t i0 = ti * 64, j0 = tj * 64;
         const uint32_t ni = f.nr - i0 < 64 ? f.nr - i0 : 64;
         const uint32_t nj = f.nr - j0 < 64 ? f.nr - j0 : 64;
@@ -362,7 +371,27 @@ struct BigGemmKernel {
         }
         for (uint32_t e = c.tid; e < nb * 64; e += c.nthr) {
             uint32_t m = e % nb, j = e / nb;
-            Rs[j * NB + m] = j < nj ? f.F[(uint64_t)(j0 + j) * f.nr + kb + m] : 0.0;
+            Rr[j * NB + m] = j < nj ? f.F[(uint64_t)(j0 + j) * f.nr + kb + lp[m]] : 0.0;
+        }
+        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
+            uint32_t i = e % nb, j = e / nb;
+            Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
+        }
+        c.sync();
+        // same operation order as BigRowPanelKernel; rows past nb come from
+        // stale shared memory and are never read
+        for (uint32_t q = c.tid; q < 256; q += c.nthr) {
+            const uint32_t i4 = (q % 8) * 4, j2 = (q / 8) * 2;
+            double acc[4][2] = {};
+            for (uint32_t m = 0; m < nb; ++m) {
+                double a[4], b[2];
+                for (int u = 0; u < 4; ++u) a[u] = Di[m * NB + i4 + u];
+                for (int v = 0; v < 2; ++v) b[v] = Rr[(j2 + v) * NB + m];
+                for (int u = 0; u < 4; ++u)
+                    for (int v = 0; v < 2; ++v) acc[u][v] += a[u] * b[v];
+            }
+            for (int v = 0; v < 2; ++v)
+                for (int u = 0; u < 4; ++u) Rs[(j2 + v) * NB + i4 + u] = acc[u][v];
         }
         c.sync();
         // 16 x 16 thread grid in the CUDA build (256 threads), 4x4 per thread;
@@ -436,28 +465,33 @@ struct BigColPanelKernel {
     }
 };
 
-/*! Column panel of step kb and pivot block of step kb + NB in ONE launch.
- * The two are independent: the column panel reads the inverted block kb and
- * writes columns kb .. kb+NB outside it, the next pivot block lies in columns
- * kb+NB ..  and was finished by the GEMM of step kb.  The pivot block is a
- * single 128-thread block per front on the critical path (~10 us of dependent
- * shared-memory round trips); run beside the column panel it costs no launch
- * of its own.  Blocks [0, nfronts) are the pivot blocks (scheduled first),
- * the rest the panel tiles. */
-struct BigColDiagKernel {
+/*! Second launch of a pivot step: the two panels of step kb and the pivot
+ * block of step kb + NB.  The three are independent once the GEMM of step kb
+ * is done: the row panel rewrites rows kb .. kb+NB, the column panel columns
+ * kb .. kb+NB (both outside the inverted block, which they only read), and
+ * the next pivot block lies in rows and columns kb+NB ..  The pivot block is
+ * a single 128-thread block per front (~10 us of dependent shared-memory
+ * round trips); beside the panels it costs no launch of its own.  Blocks
+ * [0, ndiag) are the pivot blocks (scheduled first; ndiag = 0 on the last
+ * step), then npanel column tiles, then npanel row tiles. */
+struct BigPanelsDiagKernel {
     BigColPanelKernel col;
+    BigRowPanelKernel row;
     BigDiagKernel diag;
-    uint32_t nfronts;
+    uint32_t ndiag, npanel;
     SANM_D void operator()(const rt::BlockCtx& c) const {
         rt::BlockCtx c2 = c;
-        if (c.bid < nfronts) {
+        if (c.bid < ndiag) {
             // gj32.cuh wants exactly 4 warps; warps 4..7 leave as a whole
             if (c.tid >= 128) return;
             if (c2.nthr > 128) c2.nthr = 128;
             diag(c2);
-        } else {
-            c2.bid = c.bid - nfronts;
+        } else if (c.bid < ndiag + npanel) {
+            c2.bid = c.bid - ndiag;
             col(c2);
+        } else {
+            c2.bid = c.bid - ndiag - npanel;
+            row(c2);
         }
     }
 };
@@ -779,7 +813,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.fronts.alloc(S.front_total);
     I.vecs.alloc(S.soff[S.nsn]);
     I.rowperm.alloc(n);
-    I.lperm.alloc((size_t)S.nsn * NB);
+    I.lperm.alloc((size_t)S.nsn * 2 * NB);
     I.vals.alloc(m_nnz);
     I.bp.alloc(n);
     I.xp.alloc(n);
@@ -820,7 +854,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         f.st = T.structs.ptr() + S.soff[s];
         f.inv = S.sn_parent[s] >= 0 ? T.inv.ptr() + S.inv_off[s] : nullptr;
         f.rowperm = I.rowperm.ptr() + S.sn_c0[s];
-        f.lperm = I.lperm.ptr() + (size_t)s * NB;
+        f.lperm = I.lperm.ptr() + (size_t)s * 2 * NB;
         f.gptr = T.gptr.ptr() + S.soff[s] + s;
         f.nr = S.sn_nr[s];
         f.nc = S.sn_nc[s];
@@ -983,30 +1017,24 @@ void SparseLU::factor(const double* vals_dev) {
             }
             for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
                 {
-                    LuScope ps{"lu_row"};
-                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256, panel_smem,
-                                       BigRowPanelKernel{I.fd.ptr(), list, kb, tiles});
-                }
-                {
                     LuScope ps{"lu_gemm"};
                     rt::for_each_block<256>((size_t)L.big_n * tiles * tiles, 256,
-                                       2 * NB * 64 * sizeof(double),
+                                       (3 * NB * 64 + NB * NB) * sizeof(double),
                                        BigGemmKernel{I.fd.ptr(), list, kb, tiles});
                 }
-                BigColPanelKernel col{I.fd.ptr(), list, kb, tiles};
-                if (kb + NB < L.big_max_nc) {
-                    // column panel of this step beside the pivot block of the next
-                    LuScope ps{"lu_col_diag"};
+                {
+                    // both panels of this step beside the pivot block of the next
+                    LuScope ps{"lu_panels_diag"};
+                    const uint32_t ndiag = kb + NB < L.big_max_nc ? L.big_n : 0;
+                    const uint32_t npanel = L.big_n * tiles;
                     rt::for_each_block<256>(
-                            (size_t)L.big_n * (tiles + 1), 256,
+                            (size_t)ndiag + 2 * (size_t)npanel, 256,
                             std::max(diag_smem, panel_smem),
-                            BigColDiagKernel{col,
-                                             BigDiagKernel{I.fd.ptr(), list, kb + NB, amax,
-                                                           npert},
-                                             L.big_n});
-                } else {
-                    LuScope ps{"lu_col"};
-                    rt::for_each_block<256>((size_t)L.big_n * tiles, 256, panel_smem, col);
+                            BigPanelsDiagKernel{
+                                    BigColPanelKernel{I.fd.ptr(), list, kb, tiles},
+                                    BigRowPanelKernel{I.fd.ptr(), list, kb, tiles},
+                                    BigDiagKernel{I.fd.ptr(), list, kb + NB, amax, npert},
+                                    ndiag, npanel});
                 }
             }
         }
