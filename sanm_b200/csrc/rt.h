@@ -342,6 +342,14 @@ __global__ void k_for_each_block(F f) {
 //! keeping loads in flight
 template <class F, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT > 0 ? MAXT : 1024, MINB) k_for_each_block_b(F f) {
+    // Programmatic dependent launch (for_each_block below): wait for the
+    // kernel before this one in the stream to finish and flush, THEN allow the
+    // one after it to be staged -- its blocks become resident while this grid
+    // computes and sit in their own wait, so a chain of short dependent
+    // kernels (the solver's levels and pivot steps) does not pay the launch
+    // latency per link.  Nothing is read or written before the wait.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
     run_block(f);
 }
 
@@ -411,8 +419,25 @@ void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
                 kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                 (int)smem_bytes));
     }
-    kern<<<(unsigned)nblocks, threads, smem_bytes, stream()>>>(f);
-    SANM_CUDA_CHECK(cudaGetLastError());
+    if constexpr (MAXT > 0) {
+        // SANM_NO_PDL=1: plain stream order (the kernels' griddepcontrol
+        // instructions are then no-ops)
+        static const bool pdl = getenv("SANM_NO_PDL") == nullptr;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)nblocks);
+        cfg.blockDim = dim3((unsigned)threads);
+        cfg.dynamicSmemBytes = smem_bytes;
+        cfg.stream = stream();
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        SANM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, f));
+    } else {
+        kern<<<(unsigned)nblocks, threads, smem_bytes, stream()>>>(f);
+        SANM_CUDA_CHECK(cudaGetLastError());
+    }
 }
 #endif
 
