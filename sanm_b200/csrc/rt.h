@@ -25,6 +25,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/sanm_b200.h"
@@ -243,6 +244,16 @@ public:
     size_t size() const { return m_n; }
 };
 
+/*! A block functor may split off a prologue: `auto pre(const BlockCtx&) const`
+ * reads ONLY data that no kernel writes (descriptors and lists uploaded at
+ * analysis time) and its result is passed to `operator()(c, pre)`.  The CUDA
+ * build runs it before the programmatic-dependent-launch wait, i.e. while the
+ * previous kernel of the stream is still computing. */
+template <class F, class = void>
+struct HasPre : std::false_type {};
+template <class F>
+struct HasPre<F, std::void_t<decltype(&F::pre)>> : std::true_type {};
+
 #ifdef SANM_HOSTEMU
 /* ---------------------------------------------------------------- host */
 template <class F>
@@ -268,7 +279,11 @@ void for_each_block(size_t nblocks, int /*threads*/, size_t smem_bytes,
         c.bid = b;
         c.nblk = nblocks;
         c.smem = sm.data();
-        f(c);
+        if constexpr (HasPre<F>::value) {
+            f(c, f.pre(c));
+        } else {
+            f(c);
+        }
     }
 }
 
@@ -348,9 +363,24 @@ __global__ void __launch_bounds__(MAXT > 0 ? MAXT : 1024, MINB) k_for_each_block
     // computes and sit in their own wait, so a chain of short dependent
     // kernels (the solver's levels and pivot steps) does not pay the launch
     // latency per link.  Nothing is read or written before the wait.
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    asm volatile("griddepcontrol.launch_dependents;");
-    run_block(f);
+    extern __shared__ __align__(16) char smem_raw[];
+    BlockCtx c;
+    c.tid = threadIdx.x;
+    c.nthr = blockDim.x;
+    c.bid = blockIdx.x;
+    c.nblk = gridDim.x;
+    c.smem = smem_raw;
+    if constexpr (HasPre<F>::value) {
+        // descriptor loads in flight across the wait (see HasPre)
+        auto p = f.pre(c);
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;");
+        f(c, p);
+    } else {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;");
+        f(c);
+    }
 }
 
 //! see the host build above; cooperative launch, grid = all co-resident blocks

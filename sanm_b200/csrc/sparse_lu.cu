@@ -86,9 +86,20 @@ struct AssembleChildren {
     const FrontD* fronts;
     const uint32_t* child_list;
     const Task* tasks;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const Task tk = tasks[c.bid];
-        const FrontD f = fronts[tk.front];
+    struct Pre {
+        Task tk;
+        FrontD f;
+    };
+    //! descriptors only (rt.h HasPre)
+    SANM_D Pre pre(const rt::BlockCtx& c) const {
+        Pre p;
+        p.tk = tasks[c.bid];
+        p.f = fronts[p.tk.front];
+        return p;
+    }
+    SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
+        const Task tk = p.tk;
+        const FrontD& f = p.f;
         const uint64_t total = (uint64_t)f.nr * f.nr;
         const uint64_t e0 = (uint64_t)tk.chunk * ASM_TILE;
         const uint64_t e1 = e0 + ASM_TILE < total ? e0 + ASM_TILE : total;
@@ -216,8 +227,8 @@ struct SmallFrontKernel {
     const uint32_t* list;
     const double* amax;
     int* nr_perturbed;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const FrontD f = fronts[list[c.bid]];
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid]]; }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         double* M = reinterpret_cast<double*>(c.smem);
         int* sh = reinterpret_cast<int*>(M + (uint64_t)f.nr * f.nr);
         const uint64_t tot = (uint64_t)f.nr * f.nr;
@@ -240,8 +251,10 @@ struct BigDiagKernel {
     uint32_t kb;
     const double* amax;
     int* nr_perturbed;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const FrontD f = fronts[list[c.bid]];
+    //! descriptor only (rt.h HasPre)
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid]]; }
+    SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         if (kb >= f.nc) return;
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
         double* D = reinterpret_cast<double*>(c.smem);  // nb x nb, ld NB
@@ -297,8 +310,9 @@ struct BigRowPanelKernel {
     const FrontD* fronts;
     const uint32_t* list;
     uint32_t kb, tiles;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const FrontD f = fronts[list[c.bid / tiles]];
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid / tiles]]; }
+    SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         const uint32_t tile = (uint32_t)(c.bid % tiles);
         if (kb >= f.nc || tile * 64 >= f.nr) return;
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
@@ -351,9 +365,12 @@ struct BigGemmKernel {
     const FrontD* fronts;
     const uint32_t* list;
     uint32_t kb, tiles;  // tiles per dimension
-    SANM_D void operator()(const rt::BlockCtx& c) const {
+    SANM_D FrontD pre(const rt::BlockCtx& c) const {
+        return fronts[list[c.bid / (tiles * tiles)]];
+    }
+    SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         const uint32_t per = tiles * tiles;
-        const FrontD f = fronts[list[c.bid / per]];
         const uint32_t t = (uint32_t)(c.bid % per), ti = t % tiles, tj = t / tiles;
         if (kb >= f.nc || ti * 64 >= f.nr || tj * 64 >= f.nr) return;
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
@@ -424,8 +441,9 @@ struct BigColPanelKernel {
     const FrontD* fronts;
     const uint32_t* list;
     uint32_t kb, tiles;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const FrontD f = fronts[list[c.bid / tiles]];
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid / tiles]]; }
+    SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         const uint32_t tile = (uint32_t)(c.bid % tiles);
         if (kb >= f.nc || tile * 64 >= f.nr) return;
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
@@ -479,19 +497,29 @@ struct BigPanelsDiagKernel {
     BigRowPanelKernel row;
     BigDiagKernel diag;
     uint32_t ndiag, npanel;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
+    SANM_D FrontD pre(const rt::BlockCtx& c) const {
+        rt::BlockCtx c2 = c;
+        if (c.bid < ndiag) return diag.pre(c2);
+        if (c.bid < ndiag + npanel) {
+            c2.bid = c.bid - ndiag;
+            return col.pre(c2);
+        }
+        c2.bid = c.bid - ndiag - npanel;
+        return row.pre(c2);
+    }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         rt::BlockCtx c2 = c;
         if (c.bid < ndiag) {
             // gj32.cuh wants exactly 4 warps; warps 4..7 leave as a whole
             if (c.tid >= 128) return;
             if (c2.nthr > 128) c2.nthr = 128;
-            diag(c2);
+            diag(c2, f);
         } else if (c.bid < ndiag + npanel) {
             c2.bid = c.bid - ndiag;
-            col(c2);
+            col(c2, f);
         } else {
             c2.bid = c.bid - ndiag - npanel;
-            row(c2);
+            row(c2, f);
         }
     }
 };
@@ -583,9 +611,21 @@ struct ForwardKernel {
     const Task* tasks;
     const double* b;       // right-hand side, original numbering
     const uint32_t* perm;  // new index -> original index
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const Task tk = tasks[c.bid];
-        const FrontD f = fronts[tk.front];
+    struct Pre {
+        Task tk;
+        FrontD f;
+    };
+    //! descriptors only (rt.h HasPre)
+    SANM_D Pre pre(const rt::BlockCtx& c) const {
+        Pre p;
+        p.tk = tasks[c.bid];
+        p.f = fronts[p.tk.front];
+        return p;
+    }
+    SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
+    SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
+        const Task tk = p.tk;
+        const FrontD& f = p.f;
         double* w1 = reinterpret_cast<double*>(c.smem);
         double* w1p = w1 + f.nc;
         double* part = w1p + f.nc;
@@ -633,9 +673,21 @@ struct BackwardKernel {
     double* xp;  // permuted solution
     double* x;   // solution, original numbering
     const uint32_t* perm;
-    SANM_D void operator()(const rt::BlockCtx& c) const {
-        const Task tk = tasks[c.bid];
-        const FrontD f = fronts[tk.front];
+    struct Pre {
+        Task tk;
+        FrontD f;
+    };
+    //! descriptors only (rt.h HasPre)
+    SANM_D Pre pre(const rt::BlockCtx& c) const {
+        Pre p;
+        p.tk = tasks[c.bid];
+        p.f = fronts[p.tk.front];
+        return p;
+    }
+    SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
+    SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
+        const Task tk = p.tk;
+        const FrontD& f = p.f;
         double* v = reinterpret_cast<double*>(c.smem);  // [w1' ; -x2]
         double* part = v + f.nr;
         for (uint32_t i = c.tid; i < f.nc; i += c.nthr) v[i] = f.vec[i];
