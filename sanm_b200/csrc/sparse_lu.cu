@@ -1100,8 +1100,12 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
     sanm_check(I.factored, "solve() before factor()");
     // b may alias x: the forward sweep has consumed b before the backward
     // sweep writes x
-    static const bool per_level = getenv("SANM_LU_PER_LEVEL") != nullptr;
-    if (!per_level && !g_lu_prof && m_n <= 12000) {
+    // One launch per level is the default: with programmatic dependent launch
+    // (rt.h) the chain costs ~3.5 us per level and beats the persistent
+    // grid-synchronised kernel at every size measured (cuboid n = 9 k: 0.110 vs
+    // 0.144 ms).  SANM_LU_PHASED=1 selects the persistent kernel.
+    const bool phased = getenv("SANM_LU_PHASED") != nullptr;  // per call: tests toggle it
+    if (phased && !g_lu_prof) {
         const uint32_t nlev = (uint32_t)T.levels.size();
         rt::for_each_block_phased<512>(
                 512, T.solve_smem, 2 * nlev,

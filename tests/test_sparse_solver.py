@@ -77,12 +77,17 @@ def test_zero_diagonal_small(impl):
 
 @pytest.mark.parametrize("shape,nonsym", [((5, 4, 3), 0.0), ((9, 8, 7), 0.3),
                                           ((16, 12, 10), 0.0),
-                                          # 13,824 unknowns: above the size
-                                          # where the solve switches from the
-                                          # one persistent launch to one
-                                          # launch per level
                                           ((24, 16, 12), 0.2)])
-def test_grid_blocks(impl, shape, nonsym):
+@pytest.mark.parametrize("phased", [False, True])
+def test_grid_blocks(impl, shape, nonsym, phased, monkeypatch):
+    # default: one launch per level of the supernodal forest; SANM_LU_PHASED:
+    # one persistent launch with grid barriers (read per solve() call)
+    if phased:
+        if shape == (24, 16, 12):
+            pytest.skip("one size of the opt-in path is enough")
+        monkeypatch.setenv("SANM_LU_PHASED", "1")
+    else:
+        monkeypatch.delenv("SANM_LU_PHASED", raising=False)
     rng = np.random.default_rng(11)
     A = grid_matrix(*shape, rng, nonsym=nonsym)
     n = A.shape[0]
