@@ -432,9 +432,9 @@ void AnmSolver::lu_solve(double* x, const double* b) {
 
 void AnmSolver::dot_to(int slot, const double* a, const double* b, uint64_t n) {
     const uint64_t nblk = (n + DOT_CHUNK - 1) / DOT_CHUNK;
-    rt::for_each_block(nblk, DOT_THREADS, DOT_THREADS * sizeof(double),
-                       DotPartial{a, b, n, m_d_partial.ptr()});
-    rt::for_each_block(1, DOT_THREADS, DOT_THREADS * sizeof(double),
+    rt::for_each_block<DOT_THREADS>(nblk, DOT_THREADS, DOT_THREADS * sizeof(double),
+                                    DotPartial{a, b, n, m_d_partial.ptr()});
+    rt::for_each_block<DOT_THREADS>(1, DOT_THREADS, DOT_THREADS * sizeof(double),
                        DotFinal{m_d_partial.ptr(), nblk, m_d_sc.ptr() + slot});
 }
 
@@ -654,12 +654,12 @@ void AnmSolver::solve_expansion_coeffs() {
             // libsanm/anm.cpp:266-285, evaluated after the loop
             SANM_PROF("anm_sanity_check");
             m_lu.apply(m_d_tmp.ptr(), xti);
-            rt::for_each_block(
+            rt::for_each_block<DOT_THREADS>(
                     nblk, DOT_THREADS, DOT_THREADS * sizeof(double),
                     ResidualPartial{m_d_tmp.ptr(), grad_t,
                                     i == 1 ? nullptr : m_d_bi.ptr(), sc, n,
                                     m_d_partial.ptr()});
-            rt::for_each_block(1, 32, 0,
+            rt::for_each_block<32>(1, 32, 0,
                                MaxFinal{m_d_partial.ptr(), nblk,
                                         sc + SC_CHECK0 + 2 * i});
             dot_to(SC_DOT, x1, xti, n);

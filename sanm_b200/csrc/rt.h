@@ -312,8 +312,22 @@ void for_each_block_phased(int /*threads*/, size_t smem_bytes, uint32_t nphases,
 /* ---------------------------------------------------------------- CUDA */
 template <class F>
 __global__ void k_for_each(F f, size_t n) {
+    // programmatic dependent launch, see k_for_each_block_b
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i < n) f(i);
+}
+
+//! launch attribute of the kernels that start with griddepcontrol.wait
+inline void pdl_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr) {
+    // SANM_NO_PDL=1: plain stream order (the kernels' griddepcontrol
+    // instructions are then no-ops)
+    static const bool pdl = getenv("SANM_NO_PDL") == nullptr;
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
 }
 
 template <class F, int THREADS = 128>
@@ -321,8 +335,13 @@ void for_each(size_t n, const F& f) {
     if (!n) return;
     count_launch();
     size_t blocks = (n + THREADS - 1) / THREADS;
-    k_for_each<F><<<(unsigned)blocks, THREADS, 0, stream()>>>(f, n);
-    SANM_CUDA_CHECK(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(THREADS);
+    cfg.stream = stream();
+    cudaLaunchAttribute attr[1];
+    pdl_config(cfg, attr);
+    SANM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_for_each<F>, f, n));
 }
 
 struct BlockCtx {
@@ -450,19 +469,13 @@ void for_each_block(size_t nblocks, int threads, size_t smem_bytes,
                 (int)smem_bytes));
     }
     if constexpr (MAXT > 0) {
-        // SANM_NO_PDL=1: plain stream order (the kernels' griddepcontrol
-        // instructions are then no-ops)
-        static const bool pdl = getenv("SANM_NO_PDL") == nullptr;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)nblocks);
         cfg.blockDim = dim3((unsigned)threads);
         cfg.dynamicSmemBytes = smem_bytes;
         cfg.stream = stream();
         cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = pdl ? 1 : 0;
+        pdl_config(cfg, attr);
         SANM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, f));
     } else {
         kern<<<(unsigned)nblocks, threads, smem_bytes, stream()>>>(f);
