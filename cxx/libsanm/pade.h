@@ -1,0 +1,4 @@
+// cxx/libsanm/pade.h -- forwarding header: lets sources written against the
+// reference's `#include "libsanm/pade.h"` compile against the B200 host layer.
+#pragma once
+#include "sanm_host/solvers.hpp"

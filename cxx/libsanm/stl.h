@@ -1,0 +1,5 @@
+// cxx/libsanm/stl.h -- forwarding header: lets sources written against the
+// reference's `#include "libsanm/stl.h"` compile against the B200 host layer.
+#pragma once
+#include "sanm_host/base.hpp"
+#include <algorithm>

@@ -302,6 +302,25 @@ int sanm_poly_roots(const double* f, uint64_t n, int only_real, double* re,
 int sanm_poly_solve_eqn(const double* f, uint64_t n, double xmin, double xmax,
                         double b, double eps, double* out);
 
+
+/* ---- vector Pade approximant of a series: PadeApproximation,
+ * libsanm/pade.h:20-58 (host decisions of the continuation; also what the
+ * drivers use internally).  xs is row-major [nr_coeff][len]; the last element
+ * of every row is the t coefficient.  The handle keeps its own copy. */
+typedef struct sanm_pade sanm_pade_t;
+int sanm_pade_create(const double* xs, uint64_t nr_coeff, uint64_t len,
+                     int anm_cond, int sanity_check, sanm_pade_t** out);
+int sanm_pade_destroy(sanm_pade_t* p);
+/* estimate_valid_range, pade.h:43: accepted = range larger than `start` */
+int sanm_pade_estimate_valid_range(sanm_pade_t* p, double start, double eps,
+                                   double limit, int* accepted);
+/* get_t_max / get_t_max_a, pade.h:46-49 */
+int sanm_pade_get_t_max(sanm_pade_t* p, double* t_max, double* t_max_a);
+/* solve_a, pade.h:51 */
+int sanm_pade_solve_a(sanm_pade_t* p, double t, double* out);
+/* eval_xt, pade.h:56: out has room for len doubles */
+int sanm_pade_eval_xt(sanm_pade_t* p, double a, double* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2,6 +2,7 @@
  * helpers. */
 #include "anm.h"
 #include "capi_util.h"
+#include "pade.h"
 #include "poly.h"
 #include "prof.h"
 
@@ -11,6 +12,12 @@ using namespace sanm_b200;
 
 struct sanm_anm {
     std::unique_ptr<AnmSolver> a;
+};
+
+struct sanm_pade {
+    std::vector<double> rows;  // [nr_coeff][len], owned copy of the series
+    size_t len = 0;
+    std::unique_ptr<PadeApproximation> p;
 };
 
 namespace {
@@ -201,6 +208,48 @@ int sanm_poly_solve_eqn(const double* f, uint64_t n, double xmin, double xmax,
                         double b, double eps, double* out) {
     return capi::guard([&] {
         *out = poly::solve_eqn(std::vector<double>(f, f + n), xmin, xmax, b, eps);
+    });
+}
+
+
+/* ---------------- Pade approximant (host decisions) ---------------- */
+int sanm_pade_create(const double* xs, uint64_t nr_coeff, uint64_t len,
+                     int anm_cond, int sanity_check, sanm_pade_t** out) {
+    return capi::guard([&] {
+        auto h = std::make_unique<sanm_pade>();
+        h->rows.assign(xs, xs + nr_coeff * len);
+        h->len = len;
+        std::vector<const double*> ptrs(nr_coeff);
+        for (uint64_t i = 0; i < nr_coeff; ++i)
+            ptrs[i] = h->rows.data() + i * len;
+        h->p = std::make_unique<PadeApproximation>(std::move(ptrs), len,
+                                                   anm_cond != 0,
+                                                   sanity_check != 0);
+        *out = h.release();
+    });
+}
+int sanm_pade_destroy(sanm_pade_t* p) {
+    delete p;
+    return 0;
+}
+int sanm_pade_estimate_valid_range(sanm_pade_t* p, double start, double eps,
+                                   double limit, int* accepted) {
+    return capi::guard(
+            [&] { *accepted = p->p->estimate_valid_range(start, eps, limit); });
+}
+int sanm_pade_get_t_max(sanm_pade_t* p, double* t_max, double* t_max_a) {
+    return capi::guard([&] {
+        *t_max = p->p->get_t_max();
+        *t_max_a = p->p->get_t_max_a();
+    });
+}
+int sanm_pade_solve_a(sanm_pade_t* p, double t, double* out) {
+    return capi::guard([&] { *out = p->p->solve_a(t); });
+}
+int sanm_pade_eval_xt(sanm_pade_t* p, double a, double* out) {
+    return capi::guard([&] {
+        auto v = p->p->eval_xt(a);
+        std::memcpy(out, v.data(), v.size() * sizeof(double));
     });
 }
 
