@@ -57,10 +57,12 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--energy", default="neohookean_c")
-    # per-GPU cuboid (vertices per axis); 201x51x41 -> 2.0 M tets per GPU
-    ap.add_argument("--nx", type=int, default=201)
-    ap.add_argument("--ny", type=int, default=51)
-    ap.add_argument("--nz", type=int, default=41)
+    # per-GPU cuboid (vertices per axis).  Defaults: N = 1 -> BASELINE config 5,
+    # make_cuboid(401,101,51) = 10.0 M tets; N > 1 -> 201x51x41 = 2.0 M tets
+    # per GPU (weak scaling: one cuboid N times longer in x)
+    ap.add_argument("--nx", type=int, default=None)
+    ap.add_argument("--ny", type=int, default=None)
+    ap.add_argument("--nz", type=int, default=None)
     ap.add_argument("--exchange", default="halo", choices=["halo", "allreduce"],
                     help="N > 1: halo = nodal vectors stay distributed, only "
                          "interface rows are exchanged; allreduce = every rank "
@@ -69,9 +71,17 @@ def parse_args():
                     help="skip the fea end-to-end solve section")
     ap.add_argument("--no-cpu", action="store_true",
                     help="skip the cpu_baseline leg")
-    ap.add_argument("--cpu-tets", type=int, default=120000,
-                    help="tets of the bounded CPU sample")
-    return ap.parse_args()
+    ap.add_argument("--no-energies", action="store_true",
+                    help="skip the NH-I / ARAP side measurements")
+    ap.add_argument("--cpu-tets", type=int, default=1000000,
+                    help="tets of the bounded CPU sample (an x-slab of the "
+                         "workload's cuboid, same cross-section)")
+    a = ap.parse_args()
+    big = a.gpus == 1
+    a.nx = a.nx or (401 if big else 201)
+    a.ny = a.ny or (101 if big else 51)
+    a.nz = a.nz or (51 if big else 41)
+    return a
 
 
 def algo_bytes_per_sweep(n_tets: int, energy: str, order: int = ORDER) -> float:
@@ -203,10 +213,12 @@ def load_oracle():
     return Binding(ctypes.CDLL(ORACLE_LIB), "ref_")
 
 
-def cpu_sample_dims(target_tets: int):
-    """a small cuboid of the same family with about target_tets tets"""
-    c = max(2, round((target_tets / 5 / 4) ** (1 / 3)))
-    return 4 * c + 1, c + 1, c + 1
+def cpu_sample_dims(target_tets: int, ny: int, nz: int, nx_max: int):
+    """an x-slab of the workload's cuboid (same ny x nz cross-section, same
+    spacing, material and boundary treatment) with about target_tets tets"""
+    per_layer = 5 * (ny - 1) * (nz - 1)
+    layers = min(max(2, round(target_tets / per_layer)), nx_max - 1)
+    return layers + 1, ny, nz
 
 
 class ReferenceSweep:
@@ -214,10 +226,12 @@ class ReferenceSweep:
     SparseLinearDesc::apply, oracle/ref_capi.cpp ref_sweep_run) on the host
     cores, on a small cuboid of the workload's family"""
 
-    def __init__(self, ref, energy: str, target_tets: int, threads: int):
+    def __init__(self, ref, args, threads: int):
         ref.call("set_num_threads", ctypes.c_int(threads))
         self.ref = ref
-        nx, ny, nz = cpu_sample_dims(target_tets)
+        energy = args.energy
+        self.dims = cpu_sample_dims(args.cpu_tets, args.ny, args.nz, args.nx)
+        nx, ny, nz = self.dims
         self.mesh, self.model = cuboid_model(ref, nx, ny, nz, energy)
         self.x = make_series(self.model.lt_inp.x0, ORDER)
         self.b = np.empty((ORDER + 1, self.model.lt_inp.nr_unknown_vtx))
@@ -247,22 +261,25 @@ def run_reference_arm(args):
     if rank != 0:
         return
     threads = host_threads()
-    rs = ReferenceSweep(load_oracle(), args.energy, args.cpu_tets, threads)
+    rs = ReferenceSweep(load_oracle(), args, threads)
     for _ in range(min(args.warmup, 1)):  # a CPU code needs one warm pass
         rs.run()
     times = [rs.run() for _ in range(args.steps)]
     ms = 1e3 * float(np.mean(times))
     ntet = rs.n_tets
     value = ntet * ORDER / (ms * 1e-3)
-    sample = (f"cuboid {cpu_sample_dims(args.cpu_tets)} = {ntet} tets, "
-              f"order {ORDER}, {args.energy}: same workload family, bounded")
+    sample = (f"each step = one sweep over an x-slab {rs.dims} = {ntet} tets of "
+              f"the workload's cuboid (same cross-section, spacing, material, "
+              f"order {ORDER}, {args.energy}); throughput is per tet, "
+              f"the slab bounds the run time")
+    full_tets = 5 * (args.nx - 1) * (args.ny - 1) * (args.nz - 1)
     line = {
         "impl": "reference", "metric": "tet_order_steps_per_s",
         "value": value, "unit": "tet*order/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, ntet),
+        "config": workload_config(args, full_tets, args.gpus),
         "cpu_baseline": {"value": value, "unit": "tet*order/s",
                          "cores": threads, "kind": "reference",
                          "sample": sample},
@@ -273,8 +290,8 @@ def run_reference_arm(args):
                  "unavailable on this box, not on the element path)" % threads),
     }
     emit_line(line)
-    sys.stdout.flush()
-    os._exit(0)  # skip the reference's exit-time profiler report on stdout
+    # (the reference's exit-time profiler report goes to fd 1, which main()
+    # has pointed at stderr: the process can end normally)
 
 
 def workload_config(args, tets_per_gpu, world=1):
@@ -402,6 +419,132 @@ def fea_solves(b, ref, cpu_threads):
         if "gpu" in row and "cpu_reference" in row:
             row["iters_match"] = (row["gpu"]["anm_iters"] ==
                                   row["cpu_reference"]["anm_iters"])
+    return out
+
+
+FEA_CASES = [("bob", ["bob.json"]),
+             ("armadillo_small_bend", ["armadillo_small.json",
+                                       "armadillo_small_bend_override.json"]),
+             ("cuboid_twist_order20", ["cuboid_twist.json",
+                                       "override_order20.json"]),
+             ("armadillo_small_neo_incomp", ["armadillo_small.json",
+                                             "override_neo_incomp.json"])]
+
+
+def fea_binary_solves(with_cpu: bool, mt_threads: int):
+    """The reference APPLICATION itself on both paths: cxx/_build/gpu_fea =
+    the reference's fea/*.cpp compiled unmodified against the libsanm-compatible
+    headers over libsanm_b200.so, oracle/_ref/ref_fea = the same sources on the
+    reference's libsanm (CPU; Eigen::SparseLU in place of MKL PARDISO, which is
+    not on this box).  Solve time = what the application itself reports:
+    `time_solve` of the stats JSON (fea/main.cpp:425) or the sum of the
+    `timing(sec): ... solve=` lines of a staged run (fea/main.cpp:544).  Every
+    gpu_fea run is one process, so its topology caches start cold."""
+    import re
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import fea_diff
+    if not os.path.exists(fea_diff.GPU_FEA):
+        return None
+
+    def one(binary, cfgs, sys_json="sys.json"):
+        d = tempfile.mkdtemp(prefix="bench_fea_")
+        rc, out, wall = fea_diff.run(binary, [sys_json] + cfgs, d, timeout=1500)
+        row = {"rc": rc, "wall_s": wall,
+               "anm_iters": fea_diff.iters_of(out)}
+        stage = [float(m) for m in re.findall(
+            r"timing\(sec\): prep=[0-9.eE+-]+ solve=([0-9.eE+-]+)", out)]
+        js = {}
+        for f in sorted(os.listdir(d)):
+            if f.endswith(".json"):
+                js = json.load(open(os.path.join(d, f)))
+        if "time_solve" in js:
+            row["solve_s"] = js["time_solve"]
+        elif stage:
+            row["solve_s"] = sum(stage)
+            row["stage_solve_s"] = stage
+        for k in ("displacement", "force_rms_recomp", "nr_inverted"):
+            if k in js:
+                row[k] = js[k]
+        if rc != 0:
+            row["tail"] = out[-400:]
+        import shutil
+        shutil.rmtree(d, ignore_errors=True)
+        return row
+
+    rows = []
+    for name, cfgs in FEA_CASES:
+        row = {"config": name, "gpu_fea": one(fea_diff.GPU_FEA, cfgs)}
+        rows.append(row)
+    if with_cpu and os.path.exists(fea_diff.REF_FEA):
+        for row, (name, cfgs) in zip(rows, FEA_CASES):
+            row["ref_fea"] = one(fea_diff.REF_FEA, cfgs)
+            row["ref_fea"]["threads"] = 1
+            row["iters_match"] = (row["gpu_fea"]["anm_iters"] ==
+                                  row["ref_fea"]["anm_iters"])
+            g, r = row["gpu_fea"], row["ref_fea"]
+            if "displacement" in g and "displacement" in r:
+                row["displacement_rel_diff"] = abs(
+                    g["displacement"] - r["displacement"]) / max(
+                        abs(r["displacement"]), 1e-300)
+    return rows
+
+
+def fp64_peak_tflops(torch):
+    """yardstick for the factorisation: cuBLAS DGEMM 8192^3 on this box (used
+    only as the roofline denominator)"""
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    c = torch.empty_like(a)
+    torch.matmul(a, a, out=c)
+    best = 1e30
+    for _ in range(4):
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        torch.matmul(a, a, out=c)
+        e1.record()
+        e1.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, c
+    torch.cuda.empty_cache()
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def side_energy(b, torch, stream, energy, peak, steps=5, warmup=3,
+                dims=(201, 51, 41)):
+    """the same sweep for another energy model on the 2.0 M-tet cuboid:
+    device-resident value and the step kernel's roofline fraction"""
+    from sanm_b200.capi import ElementSweep
+    mesh, model = cuboid_model(b, *dims, energy)
+    n_tets = mesh.nr_tet
+    sweep = ElementSweep(model.y, model.lt_inp.desc, model.lt_out, ORDER)
+    sweep.set_x(make_series(model.lt_inp.x0, ORDER))
+    for _ in range(warmup):
+        sweep.run()
+    torch.cuda.synchronize()
+    b.prof_reset()
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    e0.record(stream)
+    for _ in range(steps):
+        sweep.run()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    step_ms, step_launches = b.prof_get("k_fused_step")
+    S = S_MIN[energy]
+    step_algo = float(n_tets) * sum(8.0 * (S * (k + 1) + 24)
+                                    for k in range(2, ORDER + 1))
+    out = {"energy_model": energy, "tets": int(n_tets),
+           "cuboid_vertices": list(dims),
+           "value": n_tets * ORDER / (ms * 1e-3), "unit": "tet*order/s",
+           "ms_per_step": ms, "steps": steps, "warmup": warmup}
+    if step_launches:
+        ach = step_algo * steps / (step_ms * 1e-3) / 1e9
+        out["roofline"] = {"kernel": "fused.cu StepKernel", "bound": "hbm",
+                           "achieved": ach, "peak": peak, "unit": "GB/s",
+                           "frac": ach / peak,
+                           "launch_ms_avg": step_ms / step_launches}
+    del sweep
     return out
 
 
@@ -600,29 +743,65 @@ def run_ours(args):
     ref = None
     if os.path.exists(ORACLE_LIB):
         ref = load_oracle()
+    if world == 1 and not args.no_energies:
+        del sweep
+        line["energies"] = [side_energy(b, torch, stream, e, peak)
+                            for e in ("neohookean_i", "arap")
+                            if e != args.energy]
     if world == 1 and not args.no_solves:
+        fp64_peak = fp64_peak_tflops(torch)
         # before the CPU sweep below, for the reason given in fea_solves
         b.call("set_stream", ctypes.c_void_p(None))
-        line["solves"] = fea_solves(b, None if args.no_cpu else ref,
-                                    host_threads())
+        # (the CPU side of every config is the reference application itself,
+        # ref_fea, below -- not the Python front end on the oracle binding)
+        line["solves"] = fea_solves(b, None, host_threads())
+        # solver rooflines: back-solve bytes against the HBM peak,
+        # factorisation flops against the DGEMM yardstick measured just now
+        rl = []
+        for row in line["solves"]:
+            sp = row.get("gpu", {}).get("sparse")
+            if not sp:
+                continue
+            if "solve_gb_s" in sp:
+                rl.append({"config": row["config"],
+                           "kernel": "sparse_lu.cu Forward/Backward (one "
+                                     "back-solve)", "bound": "hbm",
+                           "achieved": sp["solve_gb_s"], "peak": peak,
+                           "unit": "GB/s", "frac": sp["solve_gb_s"] / peak})
+            if "factor_tflop_s" in sp:
+                rl.append({"config": row["config"],
+                           "kernel": "sparse_lu.cu numeric factorisation",
+                           "bound": "fp64", "achieved": sp["factor_tflop_s"],
+                           "peak": fp64_peak, "unit": "TFLOP/s",
+                           "frac": sp["factor_tflop_s"] / fp64_peak,
+                           "peak_source": "cuBLAS DGEMM 8192^3 measured in "
+                                          "this run (yardstick only)"})
+        line["roofline_solver"] = rl
+        # the reference application itself (unmodified fea/*.cpp) on both paths
+        fb = fea_binary_solves(not args.no_cpu, host_threads())
+        for row in fb or []:
+            dst = next((r for r in line["solves"]
+                        if r["config"] == row["config"]), None)
+            if dst is None:
+                line["solves"].append(row)
+            else:
+                dst.update({k: v for k, v in row.items() if k != "config"})
     if world == 1 and not args.no_cpu and ref is not None:
         threads = host_threads()
-        rs = ReferenceSweep(ref, args.energy, args.cpu_tets, threads)
+        rs = ReferenceSweep(ref, args, threads)
         rs.run()
         sec = min(rs.run() for _ in range(2))
         ntet = rs.n_tets
         line["cpu_baseline"] = {
             "value": ntet * ORDER / sec, "unit": "tet*order/s",
             "cores": threads, "kind": "reference",
-            "sample": (f"cuboid {cpu_sample_dims(args.cpu_tets)} = {ntet} tets,"
-                       f" order {ORDER}, {args.energy}; unmodified reference "
-                       f"ParallelTaylorCoeffProp, {threads} threads, "
-                       f"{sec:.2f} s per sweep")}
+            "sample": (f"x-slab {rs.dims} = {ntet} tets of the workload's "
+                       f"cuboid, order {ORDER}, {args.energy}; unmodified "
+                       f"reference ParallelTaylorCoeffProp, {threads} threads "
+                       f"(sys-mt{threads}), {sec:.2f} s per sweep")}
     emit_line(line)
-    sys.stdout.flush()
     if world > 1:
         dist.destroy_process_group()
-    os._exit(0)  # skip the oracle's exit-time profiler report on stdout
 
 
 _REAL_STDOUT = None

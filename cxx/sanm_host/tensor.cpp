@@ -4,8 +4,11 @@
 // nothing here is on the propagation path, which runs in libsanm_b200.so.
 #include "sanm_host/tensor.hpp"
 
+#include "sanm_b200.h"
+
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <numeric>
@@ -69,6 +72,17 @@ int get_num_threads() {
 void set_num_threads(int nr) {
     sanm_assert(nr >= 1);
     g_threads = nr;
+    // The reference brings its compute backend up before main() runs (Eigen /
+    // MKL threading in a static constructor, libsanm/tensor.cpp:24-32).  The
+    // equivalent here: create the CUDA context and load the kernel images now
+    // (fea/main.cpp:1058 calls this first thing) rather than inside the first
+    // timed solve.  SANM_DEVICE selects the GPU of this process.
+    static bool device_up = false;
+    if (!device_up) {
+        const char* dev = getenv("SANM_DEVICE");
+        capi::check(sanm_set_device(dev ? atoi(dev) : 0));
+        device_up = true;
+    }
 }
 
 TensorShape capi::shape_from(int rank, const uint64_t* dims) {

@@ -56,6 +56,24 @@ def force_rms_of(stdout):
     return [float(m) for m in re.findall(r"force rms[:=]\s*([0-9.eE+-]+)", stdout)]
 
 
+def g_quantum(v):
+    """one unit of the 6th significant digit of v (what printf %g resolves)"""
+    import math
+    return 10.0 ** (math.floor(math.log10(v)) - 5) if v > 0 else 1e-300
+
+
+def flat(v):
+    """leaves of a nested JSON value, in order"""
+    if isinstance(v, (list, tuple)):
+        for e in v:
+            yield from flat(e)
+    elif isinstance(v, dict):
+        for k in sorted(v):
+            yield from flat(v[k])
+    else:
+        yield v
+
+
 def compare(ref_dir, gpu_dir, vtx_rtol=1e-7):
     """returns (report dict, ok)"""
     rep = {"json": {}, "obj": {}}
@@ -92,6 +110,12 @@ def compare(ref_dir, gpu_dir, vtx_rtol=1e-7):
         err = max((abs(x - y) for p, q in zip(va, vb) for x, y in zip(p, q)),
                   default=0.0)
         rep["obj"][name] = err / scale
+        # the reference prints vertices with %g: differences in units of the
+        # last printed digit (6 significant digits) of the larger operand
+        rep.setdefault("obj_quanta", {})[name] = max(
+            (abs(x - y) / g_quantum(max(abs(x), abs(y)))
+             for p, q in zip(va, vb) for x, y in zip(p, q) if x != y),
+            default=0.0)
         ok &= err / scale <= vtx_rtol
     return rep, ok
 
