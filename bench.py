@@ -396,7 +396,10 @@ def fea_solves(b, ref, cpu_threads):
                       "nr_factor": e["nr_factor"],
                       "solve_ms_total": e["solve_ms"],
                       "nr_solves": e["nr_solves"],
-                      "element_ms_total": e["element_ms"]}
+                      "element_ms_total": e["element_ms"],
+                      "pade_recovered": e.get("pade_recovered"),
+                      "lu_perturbed_pivots": e.get("lu_perturbed_pivots"),
+                      "lu_refine_steps": e.get("lu_refine_steps")}
                 if e["nr_solves"] and e["solve_ms"] > 0:
                     # B_solve = 8 * nnz(L+U) + 16 n per back-solve
                     bytes_solve = 8.0 * e["factor_entries"] + 16.0 * e["n"]

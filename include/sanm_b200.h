@@ -230,6 +230,10 @@ int sanm_sparse_coeff_l2(sanm_sparse_t* s, double* out);
  * number of supernodes, number of levels of the elimination forest */
 int sanm_sparse_stats(sanm_sparse_t* s, uint64_t* nnz_lu, double* flops,
                       uint64_t* nr_supernodes, uint64_t* nr_levels);
+/* pivots perturbed by prepare() and refinement steps taken by the solves since
+ * (see sanm_anm_robustness_stats) */
+int sanm_sparse_robustness(sanm_sparse_t* s, uint64_t* nr_perturbed_pivots,
+                           uint64_t* nr_refine_steps);
 
 /* ---- ANM drivers: anm.h:98-305 -------------------------------------------- */
 /* ANMDriverHelper::HyperParam (anm.h:100-114) + ANMEqnSolver::HyperParam
@@ -293,6 +297,17 @@ int sanm_anm_lu_stats(sanm_anm_t* a, uint64_t* n, uint64_t* nnz_a,
                       uint64_t* factor_entries, double* flops,
                       uint64_t* nr_supernodes, uint64_t* nr_levels,
                       uint64_t* max_front);
+/* Robustness counters of the run so far (no reference counterpart: the
+ * reference aborts where these count).  pade_recovered: continuation steps
+ * retried from the plain series range after the consistency check of
+ * libsanm/anm.cpp:509-518 failed (only with SANM_PADE_RECOVER=1 in the
+ * environment; default = the reference's abort).  lu_perturbed_pivots /
+ * lu_refine_steps: tiny pivots statically perturbed by the last factorisation
+ * and the iterative-refinement steps its solves took because of them (what
+ * PARDISO does with the pardisoinit defaults, libsanm/sparse_solver.cpp:116). */
+int sanm_anm_robustness_stats(sanm_anm_t* a, uint64_t* pade_recovered,
+                              uint64_t* lu_perturbed_pivots,
+                              uint64_t* lu_refine_steps);
 
 /* ---- scalar polynomial helpers of the driver (host): ----------------------
  * unary_polynomial::roots / solve_eqn, libsanm/unary_polynomial.h:27-47.
@@ -318,6 +333,11 @@ int sanm_pade_estimate_valid_range(sanm_pade_t* p, double start, double eps,
 int sanm_pade_get_t_max(sanm_pade_t* p, double* t_max, double* t_max_a);
 /* solve_a, pade.h:51 */
 int sanm_pade_solve_a(sanm_pade_t* p, double t, double* out);
+/* the solved denominator coefficients (pade.h:24-25 m_d, m_d_lo; what
+ * pade.cpp:68-92 computes): d has room for nr_coeff doubles; *nr = 0 when the
+ * series was rejected at construction (pade.cpp:19-21,44-48) */
+int sanm_pade_get_denominator(sanm_pade_t* p, int lower_order, double* d,
+                              uint64_t* nr);
 /* eval_xt, pade.h:56: out has room for len doubles */
 int sanm_pade_eval_xt(sanm_pade_t* p, double a, double* out);
 

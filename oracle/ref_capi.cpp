@@ -17,10 +17,15 @@
  *   SparseLinearDesc          libsanm/anm.h:24-85
  *   SparseSolver              libsanm/sparse_solver.h:17-87 (Eigen::SparseLU shim)
  *   ANMSolverVecScale / ANMEqnSolver / ANMImplicitSolver   libsanm/anm.h:98-305
+ *   PadeApproximation         libsanm/pade.h:20-58
+ *   unary_polynomial::roots / solve_eqn   libsanm/unary_polynomial.h:27-47
+ * (this file is compiled with -fno-access-control so that the private
+ * denominator coefficients of PadeApproximation can be compared as well)
  */
 #include "libsanm/anm.h"
 #include "libsanm/oprs.h"
 #include "libsanm/sparse_solver.h"
+#include "libsanm/unary_polynomial.h"
 
 #include <chrono>
 #include <cstdint>
@@ -145,6 +150,9 @@ struct Anm {
     ANMDriverHelper* drv() {
         if (kind == 0) return vs.get();
         if (kind == 2) return im.get();
+        // private base of ANMEqnSolver (anm.h:241): reachable for the series
+        // dump of tests/test_pade_parity.py through a C-style cast
+        if (kind == 1) return (ANMSolverVecScale*)eq.get();
         return nullptr;
     }
 };
@@ -553,6 +561,83 @@ int ref_anm_implicit_fx0(Anm* a, double* out) {
     return guard([&] {
         sanm_assert(a->kind == 2);
         export_tensor(a->im->fx0(), out);
+    });
+}
+
+/* ---------------- scalar polynomial tools ----------------
+ * unary_polynomial::roots (libsanm/unary_polynomial.cpp:154-334) and
+ * solve_eqn (:101-108); same signatures as sanm_poly_* */
+int ref_poly_roots(const double* f, uint64_t n, int only_real, double* re,
+                   double* im, uint64_t* nr_roots, int* converged) {
+    return guard([&] {
+        auto r = unary_polynomial::roots({f, f + n}, only_real != 0);
+        *converged = r.valid();
+        *nr_roots = 0;
+        if (r.valid()) {
+            *nr_roots = r.val().size();
+            for (size_t i = 0; i < r.val().size(); ++i) {
+                re[i] = r.val()[i].real();
+                im[i] = r.val()[i].imag();
+            }
+        }
+    });
+}
+int ref_poly_solve_eqn(const double* f, uint64_t n, double xmin, double xmax,
+                       double b, double eps, double* out) {
+    return guard([&] {
+        *out = unary_polynomial::solve_eqn({f, f + n}, xmin, xmax, b, eps);
+    });
+}
+
+/* ---------------- PadeApproximation (libsanm/pade.h:20-58) ----------------
+ * xs: row-major [nr_coeff][len]; same signatures as sanm_pade_* */
+struct RefPade {
+    TensorArray xs;
+    std::unique_ptr<PadeApproximation> p;
+};
+int ref_pade_create(const double* xs, uint64_t nr_coeff, uint64_t len,
+                    int anm_cond, int sanity_check, RefPade** out) {
+    return guard([&] {
+        auto h = std::make_unique<RefPade>();
+        for (uint64_t i = 0; i < nr_coeff; ++i) {
+            TensorND t{TensorShape{len}};
+            memcpy(t.woptr(), xs + i * len, sizeof(double) * len);
+            h->xs.emplace_back(std::move(t));
+        }
+        h->p.reset(new PadeApproximation{h->xs, anm_cond != 0,
+                                         sanity_check != 0});
+        *out = h.release();
+    });
+}
+int ref_pade_destroy(RefPade* p) {
+    delete p;
+    return 0;
+}
+int ref_pade_estimate_valid_range(RefPade* p, double start, double eps,
+                                  double limit, int* accepted) {
+    return guard(
+            [&] { *accepted = p->p->estimate_valid_range(start, eps, limit); });
+}
+int ref_pade_get_t_max(RefPade* p, double* t_max, double* t_max_a) {
+    return guard([&] {
+        *t_max = p->p->get_t_max();
+        *t_max_a = p->p->get_t_max_a();
+    });
+}
+int ref_pade_solve_a(RefPade* p, double t, double* out) {
+    return guard([&] { *out = p->p->solve_a(t); });
+}
+int ref_pade_eval_xt(RefPade* p, double a, double* out) {
+    return guard([&] { export_tensor(p->p->eval_xt(a), out); });
+}
+/* denominator coefficients d_0..d_{n-1} (m_d) and the lower-order set
+ * (m_d_lo); *nr = 0 when the constructor rejected the series */
+int ref_pade_get_denominator(RefPade* p, int lower_order, double* d,
+                             uint64_t* nr) {
+    return guard([&] {
+        const std::vector<fp_t>& v = lower_order ? p->p->m_d_lo : p->p->m_d;
+        *nr = v.size();
+        for (size_t i = 0; i < v.size(); ++i) d[i] = v[i];
     });
 }
 

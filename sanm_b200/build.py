@@ -20,6 +20,13 @@ LIB = os.path.join(LIBDIR, "libsanm_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a",
          "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp,-Wall,-Wno-format-zero-length,-Wno-unknown-pragmas",
+         # host code at the ISA level the oracle is built for (oracle/Makefile
+         # ARCH; the reference itself builds with -march=native): GCC then
+         # contracts a*b+c into FMA in the scalar decision code (poly.cpp,
+         # pade.cpp) exactly as it does in the reference's build -- without it
+         # the Bairstow root finder differs from the oracle's at 1e-9
+         # (tests/test_pade_parity.py)
+         "-Xcompiler", "-march=x86-64-v3",
          "-x", "cu", "-Xptxas", "-v"]
 
 

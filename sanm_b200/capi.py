@@ -517,6 +517,13 @@ class _ANMBase:
                        factor_entries=u[2].value, factor_flops=fl.value,
                        nr_supernodes=w[0].value, nr_levels=w[1].value,
                        max_front=w[2].value)
+            if self.b.has("anm_robustness_stats"):
+                r = [_u64() for _ in range(3)]
+                self.b.call("anm_robustness_stats", self.h,
+                            *[C.byref(v) for v in r])
+                out.update(pade_recovered=r[0].value,
+                           lu_perturbed_pivots=r[1].value,
+                           lu_refine_steps=r[2].value)
             out["nr_solves"] = self.b.prof_get("sparse_solve")[1]
             out["nr_factor"] = self.b.prof_get("sparse_prep")[1]
         return out

@@ -137,6 +137,10 @@ public:
     };
     const Stats& stats() const { return m_stats; }
     const SparseLUStats& lu_stats() const { return m_lu.stats(); }
+    //! continuation steps retried from the plain series range after a Pade
+    //! jump failed the consistency check (only with SANM_PADE_RECOVER=1; the
+    //! reference aborts, libsanm/anm.cpp:509-518)
+    size_t nr_pade_recovered() const { return m_nr_pade_rejected; }
 
 private:
     const Kind m_kind;

@@ -173,6 +173,16 @@ int sanm_anm_lu_stats(sanm_anm_t* a, uint64_t* n, uint64_t* nnz_a,
     });
 }
 
+int sanm_anm_robustness_stats(sanm_anm_t* a, uint64_t* pade_recovered,
+                              uint64_t* lu_perturbed_pivots,
+                              uint64_t* lu_refine_steps) {
+    return capi::guard([&] {
+        *pade_recovered = a->a->nr_pade_recovered();
+        *lu_perturbed_pivots = a->a->lu_stats().nr_perturbed;
+        *lu_refine_steps = a->a->lu_stats().nr_refine_steps;
+    });
+}
+
 /* ---------------- profiler ---------------- */
 int sanm_prof_dump(char* buf, uint64_t cap) {
     return capi::guard([&] {
@@ -245,6 +255,14 @@ int sanm_pade_get_t_max(sanm_pade_t* p, double* t_max, double* t_max_a) {
 }
 int sanm_pade_solve_a(sanm_pade_t* p, double t, double* out) {
     return capi::guard([&] { *out = p->p->solve_a(t); });
+}
+int sanm_pade_get_denominator(sanm_pade_t* p, int lower_order, double* d,
+                              uint64_t* nr) {
+    return capi::guard([&] {
+        const auto& v = p->p->denominator(lower_order != 0);
+        *nr = v.size();
+        std::memcpy(d, v.data(), v.size() * sizeof(double));
+    });
 }
 int sanm_pade_eval_xt(sanm_pade_t* p, double a, double* out) {
     return capi::guard([&] {

@@ -46,4 +46,13 @@ int sanm_sparse_stats(sanm_sparse_t* s, uint64_t* nnz_lu, double* flops,
     });
 }
 
+int sanm_sparse_robustness(sanm_sparse_t* s, uint64_t* nr_perturbed_pivots,
+                           uint64_t* nr_refine_steps) {
+    return capi::guard([&] {
+        const auto& st = s->s->stats();
+        *nr_perturbed_pivots = st.nr_perturbed;
+        *nr_refine_steps = st.nr_refine_steps;
+    });
+}
+
 }  // extern "C"

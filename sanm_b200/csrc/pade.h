@@ -29,6 +29,11 @@ public:
     double solve_a(double t) const;
     //! [x(a); t(a)], pade.cpp:219-224
     std::vector<double> eval_xt(double a) const;
+    //! denominator coefficients (m_d / m_d_lo of libsanm/pade.h:24-25); empty
+    //! when the constructor rejected the series
+    const std::vector<double>& denominator(bool lower_order) const {
+        return lower_order ? m_d_lo : m_d;
+    }
 
 private:
     const bool m_sanity_check;

@@ -41,7 +41,13 @@ struct SparseLUStats {
     uint64_t front_entries = 0;   //!< sum of nr^2 (HBM held by the fronts)
     double flops = 0;             //!< flops of one numeric factorisation
     uint64_t nr_supernodes = 0, nr_levels = 0, max_front = 0;
-    uint64_t nr_perturbed = 0;    //!< tiny pivots replaced in the last factor()
+    //! tiny pivots replaced in the last factor() (static pivot perturbation,
+    //! what PARDISO does with iparm[9] = 13, libsanm/sparse_solver.cpp:116);
+    //! valid after the first solve() that follows the factorisation
+    uint64_t nr_perturbed = 0;
+    //! iterative-refinement steps taken by solve() because of them
+    //! (pardisoinit default iparm[7] = 0: refine when pivots were perturbed)
+    uint64_t nr_refine_steps = 0;
 };
 
 class SparseLU {
@@ -58,7 +64,9 @@ public:
 
     //! numeric factorisation; vals_dev: device array of CSR values (nnz)
     void factor(const double* vals_dev);
-    //! x = A^-1 b on the device (b, x: device vectors of length n; may alias)
+    //! x = A^-1 b on the device (b, x: device vectors of length n; may alias).
+    //! When the factorisation had to perturb pivots, two steps of iterative
+    //! refinement x += A^-1 (b - A x) follow.
     void solve(double* x_dev, const double* b_dev);
     //! y = A x with the CSR values of the last factor()
     void apply(double* y_dev, const double* x_dev) const;
@@ -76,6 +84,7 @@ public:
     struct Impl;
 
 private:
+    void solve_once(double* x_dev, const double* b_dev);
     std::unique_ptr<Impl> m_impl;
     bool m_analyzed = false;
     uint64_t m_n = 0, m_nnz = 0;

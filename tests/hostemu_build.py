@@ -33,7 +33,7 @@ def build(verbose=False) -> str:
                 max(os.path.getmtime(src), newest_hdr)):
             continue
         cmd = ["g++", "-std=c++17", "-O2", "-g", "-fPIC", "-fopenmp",
-               "-DSANM_HOSTEMU", "-x", "c++", "-c", src, "-o", obj, "-Wall",
+               "-DSANM_HOSTEMU", "-march=x86-64-v3", "-x", "c++", "-c", src, "-o", obj, "-Wall",
                "-Wno-format-zero-length", "-Wno-unknown-pragmas",
                "-Wno-maybe-uninitialized"]
         if verbose:

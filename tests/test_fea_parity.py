@@ -187,10 +187,14 @@ def test_implicit_solve_cuboid(impl, ref, path, monkeypatch):
 
 def test_pade_rejection_recovery(impl, monkeypatch, capfd):
     """When the consistency check of an expansion fails after a Pade jump the
-    reference aborts (libsanm/anm.cpp:509-518); this library steps back to the
-    range of the plain series and continues.  The recovery path is forced once
-    through SANM_INJECT_PADE_REJECT and must still reach t = 1 at the same
-    point as an undisturbed run."""
+    reference aborts (libsanm/anm.cpp:509-518) and so does this library by
+    default.  With SANM_PADE_RECOVER=1 it steps back to the range of the plain
+    series and continues.  The failing check is injected once through
+    SANM_INJECT_PADE_REJECT (compiled into the host-emulation build only): the
+    default must raise, the opt-in must reach t = 1 at the same point as an
+    undisturbed run."""
+    if impl.prefix != "sanm_" or "hostemu" not in impl.lib._name:
+        pytest.skip("the injection hook exists in the host-emulation build only")
     def run():
         # a displacement large enough to need several continuation steps
         _, _, model = cuboid_body(impl, (7, 3, 3), mat.NEOHOOKEAN_C, delta=6.0)
@@ -206,6 +210,9 @@ def test_pade_rejection_recovery(impl, monkeypatch, capfd):
 
     it0, x0, t0 = run()
     monkeypatch.setenv("SANM_INJECT_PADE_REJECT", "1")
+    with pytest.raises(Exception, match="injected Pade rejection"):
+        run()  # default = the reference's behaviour
+    monkeypatch.setenv("SANM_PADE_RECOVER", "1")
     it1, x1, t1 = run()
     assert "rejected" in capfd.readouterr().err
     assert it0 >= 1 and it1 >= it0
