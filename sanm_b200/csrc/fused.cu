@@ -393,7 +393,7 @@ void FusedProp::push_from(int k, const double* x, double* fx) {
         m_out_is_bias = false;
         if (fx) {
             SANM_PROF("k_assemble_final");
-            m_io->finalize(fx);
+            m_io->finalize(fx, m_local_rows);
         }
     } else {
         m_pending = k;
@@ -435,7 +435,12 @@ void FusedProp::next_bias_to(int kb, double* b) {
     sanm_check(m_io && kb >= 1 && kb <= m_K);
     if (kb == 1) {
         sanm_check(m_pending < 0);
-        rt::dzero(b, m_io->nout * sizeof(double));
+        if (m_local_rows) {
+            rt::dzero(b + m_io->row_lo,
+                      (m_io->row_hi - m_io->row_lo) * sizeof(double));
+        } else {
+            rt::dzero(b, m_io->nout * sizeof(double));
+        }
         return;
     }
     sanm_check(m_pending == kb - 1 && m_pending_x,
@@ -444,7 +449,7 @@ void FusedProp::next_bias_to(int kb, double* b) {
     m_pending = -1;
     m_pending_x = nullptr;
     SANM_PROF("k_assemble_final");
-    m_io->finalize(b);
+    m_io->finalize(b, m_local_rows);
 }
 
 void FusedProp::jacobian(double* jac) {

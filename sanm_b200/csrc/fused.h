@@ -52,6 +52,9 @@ public:
      * assembly in one kernel (plus the small second-level reduction). */
     void attach_io(std::shared_ptr<const FusedIO> io);
     bool has_io() const { return (bool)m_io; }
+    //! assembled vectors are written on the rows this rank contributes to
+    //! only (FusedIO::row_lo/row_hi); see ElementSweep::set_exchange
+    void set_local_rows(bool on) { m_local_rows = on; }
     const FusedIO* io() const { return m_io.get(); }
     void push_from(int k, const double* x, double* fx = nullptr);
     void next_bias_to(int kb, double* b);
@@ -69,6 +72,7 @@ private:
     const double* m_pending_x = nullptr;  //!< its nodal vector (fused I/O)
     std::shared_ptr<const FusedIO> m_io;
     bool m_out_is_bias = false;
+    bool m_local_rows = false;
     rt::DBuf<double> m_arena, m_aux, m_ds, m_out, m_dminv, m_xbias;
     rt::DBuf<int> m_err;
 

@@ -15,7 +15,9 @@ struct FinalizeKernel {
     const uint32_t* fin_idx;
     const double* partial;
     double* b;
-    SANM_D void operator()(size_t row) const {
+    uint64_t row0;
+    SANM_D void operator()(size_t i) const {
+        const size_t row = row0 + i;
         double s = 0;
         for (uint32_t p = fin_ptr[row], pe = fin_ptr[row + 1]; p < pe; ++p) {
             s += partial[fin_idx[p]];
@@ -29,9 +31,13 @@ constexpr uint16_t NONE16 = 0xFFFFu;
 
 }  // namespace
 
-void FusedIO::finalize(double* b) const {
-    rt::for_each(nout, FinalizeKernel{fin_ptr.ptr(), fin_idx.ptr(),
-                                      partial.ptr(), b});
+void FusedIO::finalize(double* b, bool local_only) const {
+    const uint64_t r0 = local_only ? row_lo : 0;
+    const uint64_t r1 = local_only ? row_hi : nout;
+    if (r1 > r0) {
+        rt::for_each(r1 - r0, FinalizeKernel{fin_ptr.ptr(), fin_idx.ptr(),
+                                             partial.ptr(), b, r0});
+    }
 }
 
 uint64_t FusedIO::table_bytes() const {
@@ -276,6 +282,15 @@ std::unique_ptr<FusedIO> FusedIO::analyse(const Remap& rin, const Remap& rout,
         std::vector<uint32_t> fill(fin_ptr.begin(), fin_ptr.end() - 1);
         for (uint64_t g = 0; g < R; ++g) fin_idx[fill[part_row[g]]++] = (uint32_t)g;
     }
+    io->row_lo = nout;
+    io->row_hi = 0;
+    for (uint64_t r = 0; r < nout; ++r) {
+        if (fin_ptr[r + 1] > fin_ptr[r]) {
+            io->row_lo = std::min(io->row_lo, r);
+            io->row_hi = r + 1;
+        }
+    }
+    if (io->row_lo >= io->row_hi) io->row_lo = io->row_hi = 0;
     io->h_grow = std::move(grow);
     io->nrm.upload(nrm);
     io->lrow.upload(lrow);

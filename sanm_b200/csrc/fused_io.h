@@ -49,6 +49,10 @@ struct FusedIO {
     rt::DBuf<uint32_t> fin_idx;  //!< partial ids of each output row
     rt::DBuf<double> partial;    //!< [nr_partial]
     uint64_t nr_partial = 0;
+    //! output rows that receive any contribution from these tets lie in
+    //! [row_lo, row_hi): the whole vector for a full mesh, this rank's slab
+    //! (plus its interface planes) for a pre-sharded one
+    uint64_t row_lo = 0, row_hi = 0;
     // ---- host copies for the element-wise K assembly (k_assemble.cu)
     std::vector<uint32_t> h_uidx, h_gidx;  //!< as uidx / gidx above
     std::vector<uint32_t> h_grow;          //!< [12][npad] global row of (d, c)
@@ -56,8 +60,12 @@ struct FusedIO {
     //! nullptr when either map lacks the structure described above
     static std::unique_ptr<FusedIO> analyse(const Remap& rin, const Remap& rout,
                                             uint64_t n_tets);
-    //! b[row] = sum of its partials (second level of the assembly)
-    void finalize(double* b) const;
+    //! b[row] = sum of its partials (second level of the assembly).
+    //! local_only: touch rows [row_lo, row_hi) only -- the work of a rank is
+    //! then proportional to ITS tets, not to the global mesh (rows outside
+    //! receive nothing from this rank; with distributed nodal vectors nobody
+    //! reads them here)
+    void finalize(double* b, bool local_only = false) const;
     //! bytes of index/weight tables one order step reads
     uint64_t table_bytes() const;
 };

@@ -51,6 +51,8 @@ void main_wait(void*) {}
 void pipe_wait(int, void*) {}
 void pipe_sync(int) {}
 void fence_drop(void*) {}
+ScopedPipe::ScopedPipe(int) {}
+ScopedPipe::~ScopedPipe() {}
 void* hmalloc_pinned(size_t bytes) { return malloc(bytes ? bytes : 1); }
 void hfree_pinned(void* p) { free(p); }
 
@@ -59,6 +61,7 @@ void hfree_pinned(void* p) { free(p); }
 namespace {
 cudaStream_t g_stream = nullptr, g_user_stream = nullptr;
 bool g_device_ok = false, g_use_user_stream = false;
+cudaStream_t g_override = nullptr;  //!< ScopedPipe
 }  // namespace
 
 void check_device() {
@@ -91,6 +94,7 @@ void check_device() {
 
 stream_t stream() {
     check_device();
+    if (g_override) return g_override;
     return g_use_user_stream ? g_user_stream : g_stream;
 }
 
@@ -152,7 +156,7 @@ void dzero(void* dst, size_t bytes) {
 }
 
 namespace {
-cudaStream_t g_pipe[2] = {nullptr, nullptr};
+cudaStream_t g_pipe[3] = {nullptr, nullptr, nullptr};
 cudaStream_t pipe_stream(int pipe) {
     check_device();
     if (!g_pipe[pipe]) {
@@ -191,6 +195,11 @@ void pipe_sync(int pipe) { SANM_CUDA_CHECK(cudaStreamSynchronize(pipe_stream(pip
 void fence_drop(void* fence) {
     if (fence) cudaEventDestroy(static_cast<cudaEvent_t>(fence));
 }
+ScopedPipe::ScopedPipe(int pipe) {
+    sanm_check(!g_override, "nested ScopedPipe");
+    g_override = pipe_stream(pipe);
+}
+ScopedPipe::~ScopedPipe() { g_override = nullptr; }
 
 void* hmalloc_pinned(size_t bytes) {
     check_device();

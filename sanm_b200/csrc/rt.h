@@ -162,6 +162,17 @@ void dzero(void* dst, size_t bytes);
  * expressed with fences: a fence taken on one stream can be awaited by the
  * other without blocking the host. */
 constexpr int PIPE_H2D = 0, PIPE_D2H = 1;
+//! third side stream: exchange steps (comm.cu) that run beside the element
+//! kernels of the next order
+constexpr int PIPE_COMM = 2;
+//! while alive, stream() is the given pipe: kernels and collectives launched
+//! in the scope go to the side stream (the caller orders it with fences)
+struct ScopedPipe {
+    explicit ScopedPipe(int pipe);
+    ~ScopedPipe();
+    ScopedPipe(const ScopedPipe&) = delete;
+    ScopedPipe& operator=(const ScopedPipe&) = delete;
+};
 void pipe_h2d(void* dst, const void* src, size_t bytes);  //!< async on pipe 0
 void pipe_d2h(void* dst, const void* src, size_t bytes);  //!< async on pipe 1
 //! opaque fence = everything queued so far on the main stream / on a pipe

@@ -54,6 +54,10 @@ public:
     void set_exchange(int mode) {
         sanm_check(mode == 0 || mode == 1, "exchange mode %d", mode);
         m_halo_mode = mode == 1;
+        // distributed nodal vectors: the second assembly level and the zero
+        // fills run over this rank's rows only (rows outside [b_lo, b_hi) are
+        // never read or transferred in this mode)
+        m_prop->set_local_rows(m_halo_mode);
         if (m_halo_mode && !m_halo.ready) {
             comm::halo_setup(m_halo, m_b_lo, m_b_hi, m_nout);
         }
@@ -72,6 +76,7 @@ public:
 
     void run() {
         run_impl([](int) {}, [](int) {});
+        join_exchange();
     }
 
     /*! One sweep with HOST buffers, transfers overlapped with the element
@@ -127,11 +132,12 @@ public:
                     arrived[k] = nullptr;
                 },
                 [&](int k) {
-                    rt::pipe_wait(rt::PIPE_D2H, rt::fence_main());
+                    rt::pipe_wait(rt::PIPE_D2H, b_ready_fence());
                     rt::pipe_d2h(b + (size_t)k * m_nout + blo,
                                  m_bp + (size_t)k * m_nout + blo,
                                  (bhi - blo) * sizeof(double));
                 });
+        join_exchange();
         // x_K: nothing on the main stream waits for it; keep stream order sane
         for (void*& f : arrived) {
             if (f) {
@@ -156,11 +162,34 @@ public:
     }
 
 private:
+    /*! b_k is complete on the main stream.  Halo mode: nothing on the main
+     * stream reads b_k again during this sweep (there is no solve between the
+     * orders of a sweep), so the interface exchange runs on the side stream
+     * beside the element kernels of the next orders; consumers of b_k (the
+     * device->host pipe, the end of the sweep) wait for the side stream. */
     void exchange(double* b) {
         if (m_halo_mode) {
-            comm::halo_sum(b, m_halo);
+            if (comm::world() > 1 && m_async_halo) {
+                rt::pipe_wait(rt::PIPE_COMM, rt::fence_main());
+                rt::ScopedPipe side{rt::PIPE_COMM};
+                comm::halo_sum(b, m_halo);
+                m_halo_inflight = true;
+            } else {
+                comm::halo_sum(b, m_halo);
+            }
         } else {
             comm::allreduce_sum(b, m_nout);
+        }
+    }
+    //! fence after which b_k (exchanged) may be read
+    void* b_ready_fence() {
+        return m_halo_inflight ? rt::fence_pipe(rt::PIPE_COMM) : rt::fence_main();
+    }
+    //! main stream waits for the exchanges still running on the side stream
+    void join_exchange() {
+        if (m_halo_inflight) {
+            rt::main_wait(rt::fence_pipe(rt::PIPE_COMM));
+            m_halo_inflight = false;
         }
     }
 
@@ -259,6 +288,9 @@ private:
     int m_order;
     uint64_t m_nin = 0, m_nout = 0;
     uint64_t m_x_lo = 0, m_x_hi = 0, m_b_lo = 0, m_b_hi = 0;
+    bool m_halo_inflight = false;
+    //! SANM_SYNC_HALO=1: exchange on the main stream (measurement aid)
+    const bool m_async_halo = getenv("SANM_SYNC_HALO") == nullptr;
     bool m_halo_mode = false;
     comm::Halo m_halo;
     std::unique_ptr<TaylorProp> m_prop;

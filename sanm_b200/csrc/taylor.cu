@@ -121,6 +121,7 @@ void TaylorProp::prepare(const Shape& x_shape) {
         FusedSpec spec = match_fea_graph(*m_graph, m_out_var, x_shape);
         if (spec.material != fused::MAT_NONE) {
             m_fused.reset(new FusedProp{*m_graph, spec, n, m_max_order});
+            m_fused->set_local_rows(m_local_rows);
             m_npad = m_fused->npad();
             m_arena.release();
             m_prepared = true;

@@ -54,6 +54,11 @@ public:
      * path: Remap::apply around push_xi_filled / compute_next_order_bias). */
     bool attach_io(const class Remap& rin, const class Remap& rout);
     const FusedIO* fused_io() const { return m_fused ? m_fused->io() : nullptr; }
+    //! fused I/O only: assemble on the locally touched rows alone
+    void set_local_rows(bool on) {
+        m_local_rows = on;
+        if (m_fused) m_fused->set_local_rows(on);
+    }
     //! push_xi(remap_in(x)); at order 0 also fx = remap_out(f(..)) if non-null.
     //! x must stay valid until the next compute_next_order_bias_to()
     void push_xi_from(const double* x, double* fx = nullptr);
@@ -111,6 +116,7 @@ private:
     std::vector<taylor::DOp> m_hops;
     taylor::DProgram m_prog{};
     std::unique_ptr<FusedProp> m_fused;
+    bool m_local_rows = false;
 
     void launch(int k, int phase, int sb_zero);
 };
