@@ -581,8 +581,10 @@ void AnmSolver::solve_expansion_coeffs() {
                             m_d_k2vals.alloc(m_neq->nnz2());
                             m_d_atb.alloc(n);
                         } else {
+                            // ordering hint: the current point (in `fea`
+                            // the vertex coordinates of the unknowns)
                             m_lu.analyze(n, m_kasm->rowptr().data(),
-                                         m_kasm->colidx().data());
+                                         m_kasm->colidx().data(), m_xt0.data());
                         }
                     }
                     m_d_kvals.alloc(m_kasm->nnz());

@@ -31,6 +31,19 @@ constexpr int NB = 32;          //!< pivot block of the large-front path
 constexpr uint32_t SMALL_NR = 104;  //!< fronts up to this size live in smem
 constexpr int ASM_TILE = 4096;  //!< entries per assembly task
 constexpr int ABSMAX_BLOCKS = 256;
+constexpr int LPERM_PER_FRONT = 128;  //!< >= 2 * NB (narrow path) and >= WB (wide path)
+//! fronts of at least this many rows take the superblock (DMMA) path
+//! (read at every analyze(): tests force small fronts through it)
+uint32_t wide_min_nr() {
+    const char* e = getenv("SANM_LU_WIDE_MIN");
+    return e ? (uint32_t)std::max(129, atoi(e)) : 1024u;
+}
+//! levels whose largest front has more rows than this keep the solve's work
+//! vector in global memory (L2) instead of shared memory
+uint32_t solve_smem_nr() {
+    const char* e = getenv("SANM_LU_SOLVE_SMEM_NR");
+    return e ? (uint32_t)std::max(64, atoi(e)) : 8192u;
+}
 
 struct FrontD {
     double* F;        //!< nr x nr, column-major
@@ -524,6 +537,8 @@ struct BigPanelsDiagKernel {
     }
 };
 
+#include "sparse_lu_wide.h"
+
 /* ---- solves */
 
 /* Solve kernels.  A task is one chunk of ROWS rows of one front; a block of
@@ -602,7 +617,9 @@ constexpr size_t solve_scratch_doubles() {
 
 //! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates;
 //! b is read through the fill-reducing permutation
-template <int SOLVE_ROWS, int GROUPS>
+//! VG: the front's w1' was written to f.vec[0 .. nc) by SolvePrepKernel and is
+//! read from global memory (fronts too large for a shared-memory copy)
+template <int SOLVE_ROWS, int GROUPS, bool VG = false>
 struct ForwardKernel {
     static constexpr int SOLVE_THREADS = SOLVE_ROWS * GROUPS;
     const FrontD* fronts;
@@ -627,21 +644,25 @@ struct ForwardKernel {
         const Task tk = p.tk;
         const FrontD& f = p.f;
         double* w1 = reinterpret_cast<double*>(c.smem);
-        double* w1p = w1 + f.nc;
-        double* part = w1p + f.nc;
-        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
-            // child updates in child order (flattened at analysis time: offsets
-            // into the work vectors), so the sum is the one of the tree walk
-            double v = b[perm[f.c0 + i]];
-            for (uint32_t p = f.gptr[i], pe = f.gptr[i + 1]; p < pe; ++p) v += vecs[gsrc[p]];
-            w1[i] = v;
+        const double* w1p = VG ? f.vec : w1 + f.nc;
+        double* part = VG ? w1 : w1 + 2 * (size_t)f.nc;
+        if (!VG) {
+            double* w1p_s = w1 + f.nc;
+            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
+                // child updates in child order (flattened at analysis time:
+                // offsets into the work vectors), so the sum is the one of the
+                // tree walk
+                double v = b[perm[f.c0 + i]];
+                for (uint32_t p = f.gptr[i], pe = f.gptr[i + 1]; p < pe; ++p) v += vecs[gsrc[p]];
+                w1[i] = v;
+            }
+            c.sync();
+            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
+                w1p_s[i] = w1[f.rowperm[i]];
+                if (tk.chunk == 0) f.vec[i] = w1p_s[i];
+            }
+            c.sync();
         }
-        c.sync();
-        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
-            w1p[i] = w1[f.rowperm[i]];
-            if (tk.chunk == 0) f.vec[i] = w1p[i];
-        }
-        c.sync();
         const uint32_t nu = f.nr - f.nc;
         const uint32_t r0 = tk.chunk * SOLVE_ROWS;
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
@@ -665,7 +686,9 @@ struct ForwardKernel {
 
 //! backward: x1 = G w1' - F12' x2, written to the permuted work vector (read
 //! by descendants) and to the caller's vector in original numbering
-template <int SOLVE_ROWS, int GROUPS>
+//! VG: [w1' ; -x2] is f.vec (the tail written by SolvePrepKernel), read from
+//! global memory
+template <int SOLVE_ROWS, int GROUPS, bool VG = false>
 struct BackwardKernel {
     static constexpr int SOLVE_THREADS = SOLVE_ROWS * GROUPS;
     const FrontD* fronts;
@@ -688,11 +711,14 @@ struct BackwardKernel {
     SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
         const Task tk = p.tk;
         const FrontD& f = p.f;
-        double* v = reinterpret_cast<double*>(c.smem);  // [w1' ; -x2]
-        double* part = v + f.nr;
-        for (uint32_t i = c.tid; i < f.nc; i += c.nthr) v[i] = f.vec[i];
-        for (uint32_t i = f.nc + c.tid; i < f.nr; i += c.nthr) v[i] = -xp[f.st[i]];
-        c.sync();
+        double* vs = reinterpret_cast<double*>(c.smem);  // [w1' ; -x2]
+        const double* v = VG ? f.vec : vs;
+        double* part = VG ? vs : vs + f.nr;
+        if (!VG) {
+            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) vs[i] = f.vec[i];
+            for (uint32_t i = f.nc + c.tid; i < f.nr; i += c.nthr) vs[i] = -xp[f.st[i]];
+            c.sync();
+        }
         const uint32_t r0 = tk.chunk * SOLVE_ROWS;
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
@@ -706,6 +732,48 @@ struct BackwardKernel {
             const double acc = part[lane];
             xp[f.c0 + r] = acc;
             x[perm[f.c0 + r]] = acc;
+        }
+    }
+};
+
+/*! Levels with fronts beyond the shared-memory budget (LuTopo::Level::
+ * solve_global): one extra launch per sweep builds each front's input vector
+ * once in global memory -- forward: w1' = P_r (b + child updates) into
+ * vec[0 .. nc); backward: -x2 into vec[nc .. nr) (the forward sweep's update
+ * part is dead by then) -- and the row-chunk kernels read it through L2. */
+template <bool FORWARD>
+struct SolvePrepKernel {
+    const FrontD* fronts;
+    const uint32_t* gsrc;
+    const double* vecs;
+    const Task* tasks;
+    const double* b;
+    const uint32_t* perm;
+    const double* xp;
+    struct Pre {
+        Task tk;
+        FrontD f;
+    };
+    SANM_D Pre pre(const rt::BlockCtx& c) const {
+        Pre p;
+        p.tk = tasks[c.bid];
+        p.f = fronts[p.tk.front];
+        return p;
+    }
+    SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
+        const FrontD& f = p.f;
+        const uint32_t i0 = p.tk.chunk * 256;
+        const uint32_t i1 = i0 + 256 < f.nr ? i0 + 256 : f.nr;
+        for (uint32_t i = i0 + c.tid; i < i1; i += c.nthr) {
+            if (FORWARD) {
+                if (i >= f.nc) break;
+                const uint32_t j = f.rowperm[i];
+                double v = b[perm[f.c0 + j]];
+                for (uint32_t q = f.gptr[j], qe = f.gptr[j + 1]; q < qe; ++q) v += vecs[gsrc[q]];
+                f.vec[i] = v;
+            } else if (i >= f.nc) {
+                f.vec[i] = -xp[f.st[i]];
+            }
         }
     }
 };
@@ -795,6 +863,11 @@ struct LuTopo {
         uint32_t small_off = 0, small_n = 0;  //!< list of small fronts
         uint32_t big_off = 0, big_n = 0;      //!< list of large fronts
         uint32_t big_max_nc = 0, big_max_nr = 0, small_max_nr = 0;
+        uint32_t wide_off = 0, wide_n = 0;    //!< list of wide fronts (superblock path)
+        uint32_t wide_max_nc = 0, wide_max_nr = 0;
+        //! solve: work vectors of this level's fronts stay in global memory
+        bool solve_global = false;
+        uint32_t prep_off = 0, prep_n = 0;    //!< (front, 256-row chunk) tasks
         uint32_t fwd_off = 0, fwd_n = 0, bwd_off = 0, bwd_n = 0;
         uint32_t max_nc = 0, max_nr = 0;
     };
@@ -802,8 +875,10 @@ struct LuTopo {
     rt::DBuf<Task> asm_tasks, fwd_tasks, bwd_tasks;
     rt::DBuf<LevelD> level_d;
     size_t solve_smem = 0;
-    rt::DBuf<uint32_t> small_list, big_list;
+    rt::DBuf<uint32_t> small_list, big_list, wide_list;
+    rt::DBuf<Task> prep_tasks;
     uint32_t max_front = 0;
+    uint32_t wide_min = 0, smem_nr = 0;  //!< thresholds the lists were built with
 };
 
 struct SparseLU::Impl {
@@ -825,7 +900,7 @@ const uint32_t* SparseLU::d_rowptr() const { return m_impl->topo->rowptr.ptr(); 
 const uint32_t* SparseLU::d_colidx() const { return m_impl->topo->colidx.ptr(); }
 
 void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
-                       const uint32_t* colidx) {
+                       const uint32_t* colidx, const double* node_keys) {
     rt::check_device();
     sanm_check(n > 0 && n < (1ull << 31));
     Impl& I = *m_impl;
@@ -838,18 +913,22 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     const uint64_t key = hash_bytes(
             colidx, m_nnz * sizeof(uint32_t),
             hash_bytes(rowptr, (n + 1) * sizeof(uint32_t), n * 0x51ED27ull + m_nnz));
+    const uint32_t wide_min = wide_min_nr(), smem_nr = solve_smem_nr();
     I.topo = topo_cache.get(key);
     bool fresh = false;
-    if (!I.topo || I.topo->h_rowptr.size() != n + 1 ||
+    if (!I.topo || I.topo->wide_min != wide_min || I.topo->smem_nr != smem_nr ||
+        I.topo->h_rowptr.size() != n + 1 ||
         I.topo->h_colidx.size() != m_nnz ||
         memcmp(I.topo->h_rowptr.data(), rowptr, (n + 1) * sizeof(uint32_t)) ||
         memcmp(I.topo->h_colidx.data(), colidx, m_nnz * sizeof(uint32_t))) {
         fresh = true;
         I.topo = std::make_shared<LuTopo>();
+        I.topo->wide_min = wide_min;
+        I.topo->smem_nr = smem_nr;
         I.topo->h_rowptr.assign(rowptr, rowptr + n + 1);
         I.topo->h_colidx.assign(colidx, colidx + m_nnz);
         I.topo->sym = std::make_shared<const Symbolic>(
-                symbolic_analyze((uint32_t)n, rowptr, colidx));
+                symbolic_analyze((uint32_t)n, rowptr, colidx, node_keys));
         topo_cache.put(key, I.topo);
     }
     LuTopo& T = *I.topo;
@@ -867,7 +946,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.fronts.alloc(S.front_total);
     I.vecs.alloc(S.soff[S.nsn]);
     I.rowperm.alloc(n);
-    I.lperm.alloc((size_t)S.nsn * 2 * NB);
+    I.lperm.alloc((size_t)S.nsn * LPERM_PER_FRONT);
     I.vals.alloc(m_nnz);
     I.bp.alloc(n);
     I.xp.alloc(n);
@@ -908,7 +987,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         f.st = T.structs.ptr() + S.soff[s];
         f.inv = S.sn_parent[s] >= 0 ? T.inv.ptr() + S.inv_off[s] : nullptr;
         f.rowperm = I.rowperm.ptr() + S.sn_c0[s];
-        f.lperm = I.lperm.ptr() + (size_t)s * 2 * NB;
+        f.lperm = I.lperm.ptr() + (size_t)s * LPERM_PER_FRONT;
         f.gptr = T.gptr.ptr() + S.soff[s] + s;
         f.nr = S.sn_nr[s];
         f.nc = S.sn_nc[s];
@@ -918,21 +997,23 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         f.parent = S.sn_parent[s];
         max_front = std::max(max_front, f.nr);
     }
-    sanm_check(max_front <= 13000,
-               "front of size %u exceeds the shared-memory budget of the solve "
-               "kernels", max_front);
+    sanm_check(max_front < 65536,
+               "front of %u rows: the assembly kernel indexes a front with 32 bits",
+               max_front);
     I.fd.upload(fd);
 
     const uint32_t nlev = (uint32_t)S.level_ptr.size() - 1;
     if (fresh) {
     T.levels.assign(nlev, {});
-    std::vector<Task> asm_t, fwd_t, bwd_t;
-    std::vector<uint32_t> small_l, big_l;
+    std::vector<Task> asm_t, fwd_t, bwd_t, prep_t;
+    std::vector<uint32_t> small_l, big_l, wide_l;
     for (uint32_t l = 0; l < nlev; ++l) {
         auto& L = T.levels[l];
         L.asm_off = (uint32_t)asm_t.size();
         L.small_off = (uint32_t)small_l.size();
         L.big_off = (uint32_t)big_l.size();
+        L.wide_off = (uint32_t)wide_l.size();
+        L.prep_off = (uint32_t)prep_t.size();
         L.fwd_off = (uint32_t)fwd_t.size();
         L.bwd_off = (uint32_t)bwd_t.size();
         for (uint32_t q = S.level_ptr[l]; q < S.level_ptr[l + 1]; ++q) {
@@ -947,6 +1028,10 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
             if (nr <= SMALL_NR) {
                 small_l.push_back(s);
                 L.small_max_nr = std::max(L.small_max_nr, nr);
+            } else if (nr >= wide_min) {
+                wide_l.push_back(s);
+                L.wide_max_nc = std::max(L.wide_max_nc, nc);
+                L.wide_max_nr = std::max(L.wide_max_nr, nr);
             } else {
                 big_l.push_back(s);
                 L.big_max_nc = std::max(L.big_max_nc, nc);
@@ -962,6 +1047,15 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
         L.asm_n = (uint32_t)asm_t.size() - L.asm_off;
         L.small_n = (uint32_t)small_l.size() - L.small_off;
         L.big_n = (uint32_t)big_l.size() - L.big_off;
+        L.wide_n = (uint32_t)wide_l.size() - L.wide_off;
+        L.solve_global = L.max_nr > smem_nr;
+        if (L.solve_global) {
+            for (uint32_t q = S.level_ptr[l]; q < S.level_ptr[l + 1]; ++q) {
+                const uint32_t s = S.level_list[q];
+                for (uint32_t t = 0; t * 256 < S.sn_nr[s]; ++t) prep_t.push_back({s, t});
+            }
+        }
+        L.prep_n = (uint32_t)prep_t.size() - L.prep_off;
         L.fwd_n = (uint32_t)fwd_t.size() - L.fwd_off;
         L.bwd_n = (uint32_t)bwd_t.size() - L.bwd_off;
     }
@@ -972,6 +1066,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
             const auto& L = T.levels[l];
             const bool fw = L.max_nc >= SOLVE_WIDE_COLS, bw = L.max_nr >= SOLVE_WIDE_COLS;
             ld[l] = {L.fwd_off, L.fwd_n, L.bwd_off, L.bwd_n, fw, bw};
+            if (L.solve_global) continue;  // (the persistent kernel is not used then)
             sm = std::max(sm, 2 * (size_t)L.max_nc +
                                       (fw ? solve_scratch_doubles<FWD_ROWS, FWD_GROUPS_WIDE>()
                                           : solve_scratch_doubles<FWD_ROWS, FWD_GROUPS_NARROW>()));
@@ -987,6 +1082,10 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     T.bwd_tasks.upload(bwd_t);
     T.small_list.upload(small_l);
     T.big_list.upload(big_l);
+    if (wide_l.empty()) wide_l.push_back(0);
+    T.wide_list.upload(wide_l);
+    if (prep_t.empty()) prep_t.push_back({0, 0});
+    T.prep_tasks.upload(prep_t);
     }  // fresh
 
     if (getenv("SANM_LU_DEBUG")) {
@@ -1056,6 +1155,37 @@ void SparseLU::factor(const double* vals_dev) {
                                SmallFrontKernel{I.fd.ptr(),
                                                 T.small_list.ptr() + L.small_off,
                                                 amax, npert});
+        }
+        if (L.wide_n) {
+            // superblocks of WB pivots: inverse of the pivot block, row panel,
+            // rank-WB trailing update (DMMA), column panel (sparse_lu_wide.h)
+            const uint32_t* list = T.wide_list.ptr() + L.wide_off;
+            const uint32_t tiles = (L.wide_max_nr + WT - 1) / WT;
+            for (uint32_t kb = 0; kb < L.wide_max_nc; kb += WB) {
+                {
+                    LuScope ps{"lu_wide_diag"};
+                    rt::for_each_block<512>(L.wide_n, 512, W_DIAG_SMEM,
+                                            WideDiagKernel{I.fd.ptr(), list, kb, amax, npert});
+                }
+                {
+                    LuScope ps{"lu_wide_row"};
+                    rt::for_each_block<W_GEMM_THREADS>(
+                            (size_t)L.wide_n * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
+                            WidePanelKernel<true>{I.fd.ptr(), list, kb, tiles});
+                }
+                {
+                    LuScope ps{"lu_wide_gemm"};
+                    rt::for_each_block<W_GEMM_THREADS>(
+                            (size_t)L.wide_n * tiles * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
+                            WideGemmKernel{I.fd.ptr(), list, kb, tiles});
+                }
+                {
+                    LuScope ps{"lu_wide_col"};
+                    rt::for_each_block<W_GEMM_THREADS>(
+                            (size_t)L.wide_n * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
+                            WidePanelKernel<false>{I.fd.ptr(), list, kb, tiles});
+                }
+            }
         }
         if (L.big_n) {
             const uint32_t* list = T.big_list.ptr() + L.big_off;
@@ -1154,7 +1284,8 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
     // (rt.h) the chain costs ~3.5 us per level and beats the persistent
     // grid-synchronised kernel at every size measured (cuboid n = 9 k: 0.110 vs
     // 0.144 ms).  SANM_LU_PHASED=1 selects the persistent kernel.
-    const bool phased = getenv("SANM_LU_PHASED") != nullptr;  // per call: tests toggle it
+    bool phased = getenv("SANM_LU_PHASED") != nullptr;  // per call: tests toggle it
+    for (auto& L : T.levels) phased = phased && !L.solve_global;
     if (phased && !g_lu_prof) {
         const uint32_t nlev = (uint32_t)T.levels.size();
         rt::for_each_block_phased<512>(
@@ -1169,7 +1300,19 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
         snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - T.levels.data()));
         LuScope ps{tag};
         constexpr int R = FWD_ROWS;
-        if (L.max_nc >= SOLVE_WIDE_COLS) {
+        if (L.solve_global) {
+            constexpr int G = FWD_GROUPS_WIDE;
+            rt::for_each_block<256>(
+                    L.prep_n, 256, 0,
+                    SolvePrepKernel<true>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                                          T.prep_tasks.ptr() + L.prep_off, b_dev,
+                                          T.perm.ptr(), I.xp.ptr()});
+            rt::for_each_block<R * G>(
+                    L.fwd_n, R * G, solve_scratch_doubles<R, G>() * sizeof(double),
+                    ForwardKernel<R, G, true>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                                              T.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                              T.perm.ptr()});
+        } else if (L.max_nc >= SOLVE_WIDE_COLS) {
             constexpr int G = FWD_GROUPS_WIDE;
             rt::for_each_block<R * G>(
                     L.fwd_n, R * G,
@@ -1192,7 +1335,18 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
         snprintf(tag, sizeof(tag), "lu_bwd_%02d", (int)l);
         LuScope ps{tag};
         constexpr int R = BWD_ROWS;
-        if (L.max_nr >= SOLVE_WIDE_COLS) {
+        if (L.solve_global) {
+            constexpr int G = BWD_GROUPS_WIDE;
+            rt::for_each_block<256>(
+                    L.prep_n, 256, 0,
+                    SolvePrepKernel<false>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                                           T.prep_tasks.ptr() + L.prep_off, b_dev,
+                                           T.perm.ptr(), I.xp.ptr()});
+            rt::for_each_block<R * G>(
+                    L.bwd_n, R * G, solve_scratch_doubles<R, G>() * sizeof(double),
+                    BackwardKernel<R, G, true>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
+                                               I.xp.ptr(), x_dev, T.perm.ptr()});
+        } else if (L.max_nr >= SOLVE_WIDE_COLS) {
             constexpr int G = BWD_GROUPS_WIDE;
             rt::for_each_block<R * G>(
                     L.bwd_n, R * G,

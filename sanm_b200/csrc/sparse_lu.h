@@ -58,8 +58,12 @@ public:
     /*!
      * symbolic analysis of an n x n CSR pattern (columns sorted, unique).
      * The pattern is copied; values are supplied to factor().
+     * node_keys (host, n values or null): ordering hint, see
+     * symbolic_analyze() -- the ANM drivers pass x0, whose entries are the
+     * vertex coordinates in `fea`.
      */
-    void analyze(uint64_t n, const uint32_t* rowptr, const uint32_t* colidx);
+    void analyze(uint64_t n, const uint32_t* rowptr, const uint32_t* colidx,
+                 const double* node_keys = nullptr);
     bool analyzed() const { return m_analyzed; }
 
     //! numeric factorisation; vals_dev: device array of CSR values (nnz)

@@ -1,0 +1,287 @@
+/* sanm_b200/csrc/sparse_lu_wide.h -- the wide-front path of the numeric
+ * factorisation (included by sparse_lu.cu inside its anonymous namespace).
+ *
+ * Fronts of a few thousand rows and more (the top separators of 3-D meshes:
+ * 10-20 k rows for a 1 M-tet cube) are reduced WB = 128 pivots at a time.  The
+ * block Gauss-Jordan sweep composes: sweeping a set P of pivots at once is
+ *
+ *     D   = (P_r F[P,P])^-1                 WideDiagKernel, one CTA, shared memory
+ *     R'  = D  (P_r F[P,Q])                 WidePanelKernel<ROW>   (128 x nr GEMM)
+ *     F[Q,Q] -= F[Q,P] R'                   WideGemmKernel         (rank-128 update)
+ *     C'  = -F[Q,P] D                       WidePanelKernel<COL>
+ *
+ * with Q = all other rows/columns of the front (already swept pivots
+ * included, as in any Gauss-Jordan step) and P_r the row permutation of the
+ * partial pivoting inside the 128 x 128 block.  The trailing update is a real
+ * GEMM (K = 128: 2 nr^2 128 flops for 16 nr^2 bytes of front traffic, i.e.
+ * compute-bound) and runs on the FP64 tensor path: mma.sync.m8n8k4.f64 (DMMA),
+ * operands staged in shared memory by cp.async, 128 x 128 tile per CTA, 64 x 32
+ * per warp.  tcgen05 has no FP64 kind on sm_100a; DMMA and the FMA pipe have
+ * the same peak here (37.1 vs 36.7 TFLOP/s, tools/micro/fp64_probe.cu), but a
+ * DMMA needs 1 A and 1 B double per thread for 256 multiply-adds, so the
+ * kernel is not bound by shared-memory or register bandwidth as the rank-32
+ * FMA kernels of the narrow path are.
+ *
+ * Replaces PARDISO's numeric phase for these fronts
+ * (libsanm/sparse_solver.cpp:71-127, phase 12).
+ */
+#pragma once
+
+constexpr int WB = 128;  //!< pivots per superblock
+constexpr int WT = 128;  //!< tile edge of the panel / trailing GEMMs
+constexpr int WK = 32;   //!< K chunk staged per pipeline stage
+constexpr int WLDA = WT + 4;  //!< A stage: [WK][WLDA], conflict-free fragment loads
+constexpr int WLDB = WK + 4;  //!< B stage: [WT][WLDB]
+constexpr int W_STAGE_DOUBLES = WK * WLDA + WT * WLDB;
+constexpr size_t W_GEMM_SMEM = 2 * (size_t)W_STAGE_DOUBLES * sizeof(double);
+constexpr int W_GEMM_THREADS = 256;
+
+enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
+
+/*! One CTA: C(m x n) {-=, =, = -} A(m x k) B(k x n), all column-major.
+ *   A(i, q) = Ap[q * lda + i]
+ *   B(q, j) = Bp[j * ldb + (kperm ? kperm[q] : q)]
+ *   C(i, j) = Cp[j * ldc + i]
+ * m, n <= WT, k <= WB.  Entries with local row in [rs0, rs1) or local column
+ * in [cs0, cs1) are not stored (the pivot rows / columns of the step).  C may
+ * alias A or B (the panels are updated in place): every operand element is in
+ * shared memory before the first store. */
+template <int MODE>
+SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
+                                  uint64_t lda, const double* Bp, uint64_t ldb,
+                                  const uint32_t* kperm, double* Cp, uint64_t ldc,
+                                  uint32_t m, uint32_t n, uint32_t k, uint32_t rs0,
+                                  uint32_t rs1, uint32_t cs0, uint32_t cs1) {
+#ifdef SANM_HOSTEMU
+    // same arithmetic, plain loops (one emulated thread per block)
+    double* acc = reinterpret_cast<double*>(c.smem);  // [n][m]
+    for (uint32_t j = 0; j < n; ++j) {
+        for (uint32_t i = 0; i < m; ++i) {
+            double s = 0;
+            for (uint32_t q = 0; q < k; ++q) {
+                s += Ap[(uint64_t)q * lda + i] *
+                     Bp[(uint64_t)j * ldb + (kperm ? kperm[q] : q)];
+            }
+            acc[(size_t)j * WT + i] = s;
+        }
+    }
+    for (uint32_t j = 0; j < n; ++j) {
+        if (j >= cs0 && j < cs1) continue;
+        for (uint32_t i = 0; i < m; ++i) {
+            if (i >= rs0 && i < rs1) continue;
+            double* p = Cp + (uint64_t)j * ldc + i;
+            const double s = acc[(size_t)j * WT + i];
+            if (MODE == W_SUB) {
+                *p -= s;
+            } else if (MODE == W_SET) {
+                *p = s;
+            } else {
+                *p = -s;
+            }
+        }
+    }
+#else
+    double* sm = reinterpret_cast<double*>(c.smem);
+    const int tid = c.tid, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp & 1, wn = warp >> 1;  // 2 x 4 warps, 64 x 32 each
+    const int g = lane >> 2, t4 = lane & 3;
+    double acc[8][4][2];
+#pragma unroll
+    for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+    auto stage_ptr = [&](int s) { return sm + (size_t)s * W_STAGE_DOUBLES; };
+    auto load_stage = [&](int s, uint32_t k0) {
+        double* As = stage_ptr(s);
+        double* Bs = As + WK * WLDA;
+        const uint32_t kk = k - k0 < (uint32_t)WK ? k - k0 : (uint32_t)WK;
+        // A chunk: WK columns (q) of WT rows; consecutive threads -> rows
+        for (int e = tid; e < WK * WT; e += W_GEMM_THREADS) {
+            const uint32_t q = e / WT, i = e % WT;
+            const bool ok = q < kk && i < m;
+            const double* src = ok ? Ap + (uint64_t)(k0 + q) * lda + i : Ap;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(As + q * WLDA + i);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst),
+                         "l"(src), "r"(ok ? 8 : 0)
+                         : "memory");
+        }
+        // B chunk: WT columns (j) of WK rows (q); consecutive threads -> q
+        for (int e = tid; e < WT * WK; e += W_GEMM_THREADS) {
+            const uint32_t j = e / WK, q = e % WK;
+            const bool ok = q < kk && j < n;
+            const uint32_t qq = ok ? (kperm ? kperm[k0 + q] : k0 + q) : 0;
+            const double* src = ok ? Bp + (uint64_t)j * ldb + qq : Bp;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(Bs + j * WLDB + q);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst),
+                         "l"(src), "r"(ok ? 8 : 0)
+                         : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    const uint32_t nchunk = (k + WK - 1) / WK;
+    load_stage(0, 0);
+    for (uint32_t kc = 0; kc < nchunk; ++kc) {
+        if (kc + 1 < nchunk) {
+            load_stage((kc + 1) & 1, (kc + 1) * WK);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        const double* As = stage_ptr(kc & 1);
+        const double* Bs = As + WK * WLDA;
+#pragma unroll
+        for (int ks = 0; ks < WK / 4; ++ks) {
+            double a[8], b[4];
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) {
+                a[mt] = As[(ks * 4 + t4) * WLDA + wm * 64 + mt * 8 + g];
+            }
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) {
+                b[nt] = Bs[(wn * 32 + nt * 8 + g) * WLDB + ks * 4 + t4];
+            }
+#pragma unroll
+            for (int mt = 0; mt < 8; ++mt) {
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt) {
+                    asm volatile(
+                            "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 "
+                            "{%0,%1}, {%2}, {%3}, {%0,%1};"
+                            : "+d"(acc[mt][nt][0]), "+d"(acc[mt][nt][1])
+                            : "d"(a[mt]), "d"(b[nt]));
+                }
+            }
+        }
+        __syncthreads();
+    }
+    // epilogue: thread holds C(row, col) and C(row, col + 1)
+#pragma unroll
+    for (int mt = 0; mt < 8; ++mt) {
+        const uint32_t row = wm * 64 + mt * 8 + g;
+        if (row >= m || (row >= rs0 && row < rs1)) continue;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t col = wn * 32 + nt * 8 + 2 * t4 + h;
+                if (col >= n || (col >= cs0 && col < cs1)) continue;
+                double* p = Cp + (uint64_t)col * ldc + row;
+                const double s = acc[mt][nt][h];
+                if (MODE == W_SUB) {
+                    *p -= s;
+                } else if (MODE == W_SET) {
+                    *p = s;
+                } else {
+                    *p = -s;
+                }
+            }
+        }
+    }
+#endif
+}
+
+//! [a0, a1) intersected with the tile [t0, t0 + WT), in tile-local indices
+SANM_HD inline void wide_clip(uint32_t a0, uint32_t a1, uint32_t t0, uint32_t* lo,
+                              uint32_t* hi) {
+    const uint32_t t1 = t0 + WT;
+    const uint32_t b0 = a0 > t0 ? a0 : t0, b1 = a1 < t1 ? a1 : t1;
+    if (b0 < b1) {
+        *lo = b0 - t0;
+        *hi = b1 - t0;
+    } else {
+        *lo = *hi = 0;
+    }
+}
+
+//! D = (P_r F[P,P])^-1 in shared memory, one CTA per front; records the row
+//! permutation (lperm: position i of the block holds original row lperm[i])
+struct WideDiagKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb;
+    const double* amax;
+    int* nr_perturbed;
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid]]; }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
+        if (kb >= f.nc) return;
+        const uint32_t wb = f.nc - kb < (uint32_t)WB ? f.nc - kb : (uint32_t)WB;
+        double* M = reinterpret_cast<double*>(c.smem);  // [wb][WB]
+        uint32_t* lperm = reinterpret_cast<uint32_t*>(M + (size_t)WB * WB);
+        int* sh = reinterpret_cast<int*>(lperm + WB);
+        double* G = f.F + (uint64_t)kb * f.nr + kb;
+        for (uint32_t e = c.tid; e < wb * wb; e += c.nthr) {
+            const uint32_t i = e % wb, j = e / wb;
+            M[j * WB + i] = G[(uint64_t)j * f.nr + i];
+        }
+        for (uint32_t i = c.tid; i < wb; i += c.nthr) lperm[i] = i;
+        c.sync();
+        gj_steps(c, M, WB, wb, 0, wb, wb, lperm, sh, amax[0] * 1e-13, nr_perturbed);
+        for (uint32_t e = c.tid; e < wb * wb; e += c.nthr) {
+            const uint32_t i = e % wb, j = e / wb;
+            G[(uint64_t)j * f.nr + i] = M[j * WB + i];
+        }
+        for (uint32_t i = c.tid; i < wb; i += c.nthr) {
+            f.lperm[i] = lperm[i];
+            f.rowperm[kb + i] = kb + lperm[i];
+        }
+    }
+};
+constexpr size_t W_DIAG_SMEM =
+        (size_t)WB * WB * sizeof(double) + WB * sizeof(uint32_t) + 16;
+
+//! ROW: R' = D (P_r R) on one 128-column tile; COL: C' = -C D on one 128-row tile
+template <bool ROW>
+struct WidePanelKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb, tiles;
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid / tiles]]; }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
+        const uint32_t t0 = (uint32_t)(c.bid % tiles) * WT;
+        if (kb >= f.nc || t0 >= f.nr) return;
+        const uint32_t wb = f.nc - kb < (uint32_t)WB ? f.nc - kb : (uint32_t)WB;
+        const uint32_t ext = f.nr - t0 < (uint32_t)WT ? f.nr - t0 : (uint32_t)WT;
+        uint32_t s0, s1;
+        wide_clip(kb, kb + wb, t0, &s0, &s1);
+        if (s1 - s0 == ext) return;  // the tile is the pivot block itself
+        double* D = f.F + (uint64_t)kb * f.nr + kb;
+        if (ROW) {
+            double* R = f.F + (uint64_t)t0 * f.nr + kb;  // rows kb.., columns t0..
+            wide_gemm_tile<W_SET>(c, D, f.nr, R, f.nr, f.lperm, R, f.nr, wb, ext, wb,
+                                  0, 0, s0, s1);
+        } else {
+            double* C = f.F + (uint64_t)kb * f.nr + t0;  // rows t0.., columns kb..
+            wide_gemm_tile<W_SETNEG>(c, C, f.nr, D, f.nr, nullptr, C, f.nr, ext, wb,
+                                     wb, s0, s1, 0, 0);
+        }
+    }
+};
+
+//! F[Q,Q] -= F[Q,P] R' on one 128 x 128 tile
+struct WideGemmKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb, tiles;
+    SANM_D FrontD pre(const rt::BlockCtx& c) const {
+        return fronts[list[c.bid / ((size_t)tiles * tiles)]];
+    }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
+        const uint32_t t = (uint32_t)(c.bid % ((size_t)tiles * tiles));
+        const uint32_t i0 = (t % tiles) * WT, j0 = (t / tiles) * WT;
+        if (kb >= f.nc || i0 >= f.nr || j0 >= f.nr) return;
+        const uint32_t wb = f.nc - kb < (uint32_t)WB ? f.nc - kb : (uint32_t)WB;
+        const uint32_t mi = f.nr - i0 < (uint32_t)WT ? f.nr - i0 : (uint32_t)WT;
+        const uint32_t nj = f.nr - j0 < (uint32_t)WT ? f.nr - j0 : (uint32_t)WT;
+        uint32_t rs0, rs1, cs0, cs1;
+        wide_clip(kb, kb + wb, i0, &rs0, &rs1);
+        wide_clip(kb, kb + wb, j0, &cs0, &cs1);
+        if (rs1 - rs0 == mi || cs1 - cs0 == nj) return;  // nothing to store
+        wide_gemm_tile<W_SUB>(c, f.F + (uint64_t)kb * f.nr + i0, f.nr,
+                              f.F + (uint64_t)j0 * f.nr + kb, f.nr, nullptr,
+                              f.F + (uint64_t)j0 * f.nr + i0, f.nr, mi, nj, wb, rs0,
+                              rs1, cs0, cs1);
+    }
+};

@@ -11,6 +11,8 @@
 #include "rt.h"
 
 #include <algorithm>
+#include <cmath>
+#include <limits>
 #include <atomic>
 #include <numeric>
 
@@ -176,6 +178,9 @@ Adj compress_graph(const Adj& a, const std::vector<u32>& sv, u32 nsv,
 class NestedDissection {
     const Adj& g;
     const std::vector<u32>& w;
+    //! optional node coordinates [ngeo][n] (hint: further bisection keys)
+    const double* geo = nullptr;
+    int ngeo = 0;
     std::vector<u32> region;  //!< region id of each node (current partition)
     std::vector<u32> level;   //!< scratch: BFS level
     std::vector<u32>& order;
@@ -473,6 +478,29 @@ class NestedDissection {
                     }
                     take(best_cut(nodes_bfs, r, wt));
                 }
+                // Geometric candidates (only with a coordinate hint): thresholds
+                // of each coordinate, i.e. axis-aligned planes.  On lattice-like
+                // bodies the distance-based keys above give diagonal cuts, whose
+                // vertex separators are about twice as heavy (a cube of 41^3
+                // nodes: 10.9 k rows in the top separator instead of 5.0 k, an
+                // order of magnitude in factorisation flops).
+                for (int ax = 0; ax < ngeo; ++ax) {
+                    const double* cx = geo + (size_t)ax * g.n();
+                    double lo = cx[nodes_bfs[0]], hi = lo;
+                    for (u32 v : nodes_bfs) {
+                        lo = std::min(lo, cx[v]);
+                        hi = std::max(hi, cx[v]);
+                    }
+                    if (!(hi > lo)) continue;
+                    // resolution: a few keys per node along the axis
+                    const double q_steps = std::min(
+                            8192.0, 4.0 * std::cbrt((double)nodes_bfs.size()) + 8.0);
+                    const double scale = q_steps / (hi - lo);
+                    for (u32 v : nodes_bfs) {
+                        key[v] = (int32_t)std::floor((cx[v] - lo) * scale + 0.5);
+                    }
+                    take(best_cut(nodes_bfs, r, wt));
+                }
                 for (size_t q = 0; q < nodes_bfs.size(); ++q) key[nodes_bfs[q]] = keep[q];
             }
             if (!cut1.valid) {
@@ -556,8 +584,9 @@ class NestedDissection {
 
 public:
     NestedDissection(const Adj& g_, const std::vector<u32>& w_,
-                     std::vector<u32>& order_)
-            : g{g_}, w{w_}, order{order_} {
+                     std::vector<u32>& order_, const double* geo_ = nullptr,
+                     int ngeo_ = 0)
+            : g{g_}, w{w_}, geo{geo_}, ngeo{ngeo_}, order{order_} {
         const u32 n = g.n();
         region.assign(n, 1);
         next_region = 2;
@@ -584,7 +613,7 @@ public:
 }  // namespace
 
 Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
-                          const uint32_t* colidx) {
+                          const uint32_t* colidx, const double* node_keys) {
     StageTimer stage_timer;
     Symbolic S;
     S.n = n;
@@ -598,7 +627,64 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
     std::vector<u32> weight;
     Adj cg = compress_graph(adj, sv, nsv, weight);
     std::vector<u32> corder;
-    { NestedDissection nd{cg, weight, corder}; }
+    // Coordinate hint: the keys of the members of a 3-unknown supervariable,
+    // in index order, are taken as the coordinates of that node (the unknowns
+    // of `fea` are the free vertex coordinates, three per vertex, and the
+    // three share one adjacency).  Nodes of any other size get the average of
+    // their neighbours.  Without enough such nodes the hint is ignored.
+    std::vector<double> geo;
+    int ngeo = 0;
+    if (node_keys && getenv("SANM_ND_NO_GEOMETRY") == nullptr) {
+        constexpr double MISSING = std::numeric_limits<double>::quiet_NaN();
+        geo.assign((size_t)3 * nsv, MISSING);
+        std::vector<uint8_t> cnt(nsv, 0);
+        u32 full = 0;
+        for (u32 i = 0; i < n; ++i) {  // members in increasing index order
+            const u32 s = sv[i];
+            if (weight[s] == 3 && cnt[s] < 3 && std::isfinite(node_keys[i])) {
+                geo[(size_t)cnt[s] * nsv + s] = node_keys[i];
+                if (++cnt[s] == 3) ++full;
+            }
+        }
+        if ((u64)full * 2 >= nsv) {
+            ngeo = 3;
+            std::vector<u32> todo;
+            for (u32 s = 0; s < nsv; ++s) {
+                if (cnt[s] != 3) {
+                    for (int k = 0; k < 3; ++k) geo[(size_t)k * nsv + s] = MISSING;
+                    todo.push_back(s);
+                }
+            }
+            for (int sweep = 0; sweep < 8 && !todo.empty(); ++sweep) {
+                std::vector<u32> rest;
+                std::vector<double> vals;
+                for (u32 s : todo) {
+                    double acc[3] = {0, 0, 0};
+                    u32 m = 0;
+                    for (auto p = cg.begin(s); p != cg.end(s); ++p) {
+                        if (std::isnan(geo[*p])) continue;
+                        for (int k = 0; k < 3; ++k) acc[k] += geo[(size_t)k * nsv + *p];
+                        ++m;
+                    }
+                    if (!m) {
+                        rest.push_back(s);
+                    } else {
+                        vals.push_back((double)s);
+                        for (int k = 0; k < 3; ++k) vals.push_back(acc[k] / m);
+                    }
+                }
+                for (size_t q = 0; q < vals.size(); q += 4) {
+                    const u32 s = (u32)vals[q];
+                    for (int k = 0; k < 3; ++k) geo[(size_t)k * nsv + s] = vals[q + 1 + k];
+                }
+                todo.swap(rest);
+            }
+            for (u32 s : todo) {
+                for (int k = 0; k < 3; ++k) geo[(size_t)k * nsv + s] = 0.0;
+            }
+        }
+    }
+    { NestedDissection nd{cg, weight, corder, ngeo ? geo.data() : nullptr, ngeo}; }
     std::vector<u32> cpos(nsv);
     for (u32 i = 0; i < nsv; ++i) cpos[corder[i]] = i;
     // expand: members of a supervariable stay adjacent
@@ -703,8 +789,20 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         u32 c0, nc, nr;
     };
     std::vector<SN> sns;
+    // Width cap: the block Gauss-Jordan of a front costs 2 nr^2 nc flops (it
+    // sweeps the whole nr x nr block per pivot), so a long fundamental chain
+    // is cheaper as several fronts of at most `max_nc` pivots each --
+    // 2 sum_i nr_i^2 nc_i approaches the 2/3 nr^3 of an LU as the pieces
+    // shrink -- at the price of one square front per piece.  Only the top
+    // separators of large 3-D problems are that wide (a 61^3-node cube: root
+    // chain of 18.7 k pivots, 1.3e13 -> 5.8e12 flops).
+    static const u32 max_nc = [] {
+        const char* e = getenv("SANM_LU_MAX_SN");
+        return e ? (u32)std::max(64, atoi(e)) : 4096u;
+    }();
     for (u32 j = 0; j < n; ++j) {
-        bool join = j > 0 && parent[j - 1] == (int32_t)j && cc[j - 1] == cc[j] + 1;
+        bool join = j > 0 && parent[j - 1] == (int32_t)j && cc[j - 1] == cc[j] + 1 &&
+                    sns.back().nc < max_nc;
         if (join) {
             ++sns.back().nc;
         } else {
@@ -729,6 +827,7 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
             SN& b = sns[p];
             if (a.c0 + a.nc != b.c0) continue;
             u64 nc2 = (u64)a.nc + b.nc, nr2 = (u64)a.nc + b.nr;
+            if (nc2 > max_nc) continue;
             u64 before = (u64)a.nr * a.nc + (u64)b.nr * b.nc;
             u64 after = nr2 * nc2;
             u64 zeros = after - before;

@@ -45,8 +45,15 @@ struct Symbolic {
 /*!
  * \param rowptr,colidx CSR pattern (n rows), columns sorted and unique; it is
  *      symmetrised internally
+ * \param node_keys optional ordering hint, one value per unknown (or null):
+ *      where three unknowns share one adjacency (the three coordinates of a
+ *      mesh vertex) their values are read as that node's position, and
+ *      axis-aligned planes join the candidate bisections of the nested
+ *      dissection.  A hint never makes the result invalid; candidates are
+ *      compared by separator weight.
  */
 Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
-                          const uint32_t* colidx);
+                          const uint32_t* colidx,
+                          const double* node_keys = nullptr);
 
 }  // namespace sanm_b200

@@ -116,3 +116,47 @@ def test_row_order_and_small_drop(impl):
     s.prepare()
     np.testing.assert_allclose(s.solve([2., 3., 4.]), [1, 1, 1], atol=1e-14)
     assert abs(s.coeff_l2() - np.sqrt(4 + 9 + 16)) < 1e-14
+
+
+@pytest.mark.parametrize("shape,nonsym", [((9, 8, 7), 0.3), ((16, 12, 10), 0.0),
+                                          ((24, 16, 12), 0.2)])
+def test_wide_front_path(impl, shape, nonsym, monkeypatch):
+    """the superblock path of large fronts (128 pivots per step: shared-memory
+    inverse of the pivot block, DMMA panels and rank-128 trailing update,
+    csrc/sparse_lu_wide.h) and the solve variant that keeps a front's work
+    vector in global memory, both forced onto small fronts through their
+    thresholds; same residual / solution bars as the default path"""
+    monkeypatch.setenv("SANM_LU_WIDE_MIN", "129")
+    monkeypatch.setenv("SANM_LU_SOLVE_SMEM_NR", "200")
+    rng = np.random.default_rng(13)
+    A = grid_matrix(*shape, rng, nonsym=nonsym)
+    n = A.shape[0]
+    s = build(impl, A).prepare()
+    for _ in range(2):
+        b = rng.uniform(-1, 1, n)
+        x = s.solve(b)
+        r = A @ x - b
+        scale = abs(A).sum(axis=1).max() * np.abs(x).max() + np.abs(b).max()
+        assert np.abs(r).max() <= 1e-12 * scale
+        xr = spla.spsolve(A.tocsc(), b)
+        assert np.abs(x - xr).max() <= 1e-10 * np.abs(xr).max()
+
+
+@pytest.mark.gpu
+def test_large_system_gpu(cuda_impl, monkeypatch):
+    """n = 140 k unknowns, nonsymmetric values: fronts of several thousand rows
+    (wide path by default), top levels solved with global work vectors;
+    residual bar of SURVEY 8c.  GPU only (5e11 flops)."""
+    monkeypatch.setenv("SANM_LU_SOLVE_SMEM_NR", "3000")
+    rng = np.random.default_rng(17)
+    A = grid_matrix(36, 36, 36, rng, nonsym=0.2)
+    n = A.shape[0]
+    s = build(cuda_impl, A).prepare()
+    st = s.stats()
+    assert st["flops"] > 1e11
+    for _ in range(2):
+        b = rng.uniform(-1, 1, n)
+        x = s.solve(b)
+        r = A @ x - b
+        scale = abs(A).sum(axis=1).max() * np.abs(x).max() + np.abs(b).max()
+        assert np.abs(r).max() <= 1e-12 * scale
