@@ -82,6 +82,9 @@ void set_num_threads(int nr) {
         const char* dev = getenv("SANM_DEVICE");
         capi::check(sanm_set_device(dev ? atoi(dev) : 0));
         device_up = true;
+        // the reference prints its profiler tags at exit; so does this layer
+        // (host wall time and the library's device time per tag)
+        ScopedProfiler::get_node();
     }
 }
 

@@ -297,6 +297,14 @@ int sanm_anm_lu_stats(sanm_anm_t* a, uint64_t* n, uint64_t* nnz_a,
                       uint64_t* factor_entries, double* flops,
                       uint64_t* nr_supernodes, uint64_t* nr_levels,
                       uint64_t* max_front);
+/* The tangent matrix K = R_out blockdiag(J_e) R_in of the last expansion, as
+ * assembled on the device: what the reference hands to SparseSolver (libsanm/
+ * anm.cpp:362-438; implicit solver: without the grad_t column, :520-608;
+ * cf. SparseSolver::dump, sparse_solver.h:76-80).  Structural pattern with
+ * explicit zeros (the reference drops |v| < 1e-9, sparse_solver.cpp:291-293).
+ * Call with null arrays to get n and nnz first; rowptr has n + 1 entries. */
+int sanm_anm_k_csr(sanm_anm_t* a, uint64_t* n, uint64_t* nnz, uint32_t* rowptr,
+                   uint32_t* colidx, double* vals);
 /* Robustness counters of the run so far (no reference counterpart: the
  * reference aborts where these count).  pade_recovered: continuation steps
  * retried from the plain series range after the consistency check of

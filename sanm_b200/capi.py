@@ -500,6 +500,33 @@ class _ANMBase:
             ret.append(v)
         return ret
 
+    def k_csr(self):
+        """the tangent matrix of the last expansion as a scipy CSR matrix:
+        ``sanm_anm_k_csr`` here, the matrix last handed to SparseSolver::
+        prepare for the oracle (``ref_last_prepared_csr``)"""
+        import scipy.sparse as sp
+        n, nnz = _u64(), _u64()
+        if self.b.prefix == "ref_":
+            self.b.call("last_prepared_csr", C.byref(n), C.byref(nnz), None,
+                        None, None)
+            ia = np.empty(n.value + 1, dtype=np.int32)
+            ja = np.empty(nnz.value, dtype=np.int32)
+            a = np.empty(nnz.value)
+            self.b.call("last_prepared_csr", C.byref(n), C.byref(nnz),
+                        ia.ctypes.data_as(C.c_void_p),
+                        ja.ctypes.data_as(C.c_void_p), _ptr(a))
+        else:
+            self.b.call("anm_k_csr", self.h, C.byref(n), C.byref(nnz), None,
+                        None, None)
+            ia = np.empty(n.value + 1, dtype=np.uint32)
+            ja = np.empty(nnz.value, dtype=np.uint32)
+            a = np.empty(nnz.value)
+            self.b.call("anm_k_csr", self.h, C.byref(n), C.byref(nnz),
+                        ia.ctypes.data_as(C.c_void_p),
+                        ja.ctypes.data_as(C.c_void_p), _ptr(a))
+        return sp.csr_matrix((a, ja.astype(np.int64), ia.astype(np.int64)),
+                             shape=(n.value, n.value))
+
     def element_stats(self):
         vals = [C.c_double() for _ in range(5)]
         self.b.call("anm_element_stats", self.h, *[C.byref(v) for v in vals])

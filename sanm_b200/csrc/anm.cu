@@ -821,6 +821,18 @@ void AnmSolver::update_approx() {
     solve_expansion_coeffs();
 }
 
+void AnmSolver::k_csr(uint64_t* n, uint64_t* nnz, uint32_t* rowptr,
+                      uint32_t* colidx, double* vals) const {
+    sanm_check(m_kasm, "k_csr() before the first expansion");
+    const auto& rp = m_kasm->rowptr();
+    const auto& ci = m_kasm->colidx();
+    *n = rp.size() - 1;
+    *nnz = ci.size();
+    if (rowptr) std::memcpy(rowptr, rp.data(), rp.size() * sizeof(uint32_t));
+    if (colidx) std::memcpy(colidx, ci.data(), ci.size() * sizeof(uint32_t));
+    if (vals) rt::d2h(vals, m_d_kvals.ptr(), ci.size() * sizeof(double));
+}
+
 void AnmSolver::eval(double a, double* x_out, double* t_out) const {
     std::vector<double> xt = eval_xt(a);
     std::memcpy(x_out, xt.data(), m_n * sizeof(double));

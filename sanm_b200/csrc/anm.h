@@ -141,6 +141,12 @@ public:
     //! jump failed the consistency check (only with SANM_PADE_RECOVER=1; the
     //! reference aborts, libsanm/anm.cpp:509-518)
     size_t nr_pade_recovered() const { return m_nr_pade_rejected; }
+    //! the tangent matrix K of the last expansion as assembled on the device
+    //! (what the reference hands to SparseSolver::prepare, libsanm/anm.cpp:
+    //! 362-438 / 520-608); rowptr has n + 1 entries.  Pointers may be null to
+    //! query the sizes only.
+    void k_csr(uint64_t* n, uint64_t* nnz, uint32_t* rowptr, uint32_t* colidx,
+               double* vals) const;
 
 private:
     const Kind m_kind;

@@ -173,6 +173,10 @@ int sanm_anm_lu_stats(sanm_anm_t* a, uint64_t* n, uint64_t* nnz_a,
     });
 }
 
+int sanm_anm_k_csr(sanm_anm_t* a, uint64_t* n, uint64_t* nnz, uint32_t* rowptr,
+                   uint32_t* colidx, double* vals) {
+    return capi::guard([&] { a->a->k_csr(n, nnz, rowptr, colidx, vals); });
+}
 int sanm_anm_robustness_stats(sanm_anm_t* a, uint64_t* pade_recovered,
                               uint64_t* lu_perturbed_pivots,
                               uint64_t* lu_refine_steps) {

@@ -34,7 +34,13 @@ CASES = {
                              "override_order20.json"],
     "armadillo_small_neo_incomp": ["sys.json", "armadillo_small.json",
                                    "override_neo_incomp.json"],
+    # the inverse problem (rest shape from the deformed one: make_inverse,
+    # fea/mesh_template.h:172-189, Cauchy-stress graphs of fea/material.cpp:20-53)
+    # with the FEA_INVCHECK round trip of fea/main.cpp:299-309: the forward
+    # problem is solved again on the recovered rest shape
+    "bob_inverse": ["sys.json", "bob.json", "override_inverse.json"],
 }
+EXTRA_ENV = {"bob_inverse": {"FEA_INVCHECK": "1"}}
 # relative bar on full-precision scalars of the stats JSON
 RTOL_STATS = 1e-7
 # .obj vertices are printed with %g: a 1e-8 difference can flip the 6th
@@ -60,12 +66,14 @@ def need_binaries():
 def run_pair(name, tmp_path, lib_dir=None):
     need_binaries()
     env = dict(os.environ)
+    env.update(EXTRA_ENV.get(name, {}))
+    env_ref = dict(env)
     if lib_dir:
         env["LD_LIBRARY_PATH"] = lib_dir + ":" + env.get("LD_LIBRARY_PATH", "")
     # the timing sections are irrelevant here; keep the oracle single-threaded
     # as config/sys.json prescribes
     rdir, gdir = str(tmp_path / "ref"), str(tmp_path / "gpu")
-    rc_r, out_r, _ = fea_diff.run(fea_diff.REF_FEA, CASES[name], rdir)
+    rc_r, out_r, _ = fea_diff.run(fea_diff.REF_FEA, CASES[name], rdir, env_ref)
     assert rc_r == 0, out_r[-3000:]
     rc_g, out_g, _ = fea_diff.run(fea_diff.GPU_FEA, CASES[name], gdir, env)
     assert rc_g == 0, out_g[-3000:]
@@ -104,18 +112,30 @@ def check_pair(name, tmp_path, lib_dir=None):
     if len(it_r) != len(it_g) or any(abs(a - b) > slack
                                      for a, b in zip(it_r, it_g)):
         msgs.append(f"ANM iterations per stage: ref {it_r} vs gpu {it_g}")
+    if name in EXTRA_ENV:
+        # "invcheck norm: %g" (fea/main.cpp:308): distance of the round trip
+        # from the original mesh; both paths must close the loop
+        import re
+        nr = [float(v) for v in re.findall(r"invcheck norm: ([0-9.eE+-]+)", out_r)]
+        ng = [float(v) for v in re.findall(r"invcheck norm: ([0-9.eE+-]+)", out_g)]
+        if len(nr) != 1 or len(ng) != 1:
+            msgs.append(f"invcheck lines: ref {nr} gpu {ng}")
+        elif ng[0] > max(10 * nr[0], 1e-8):
+            msgs.append(f"invcheck norm: ref {nr[0]} gpu {ng[0]}")
     assert not msgs, "\n".join(msgs)
     return it_r, it_g
 
 
-def test_hostemu_bob(tmp_path, hostemu):
+@pytest.mark.parametrize("name", ["bob", "bob_inverse"])
+def test_hostemu(name, tmp_path, hostemu):
     """CPU container: gpu_fea over the host-emulation build of the same kernel
-    sources (kernel logic + the whole C++ host layer), Bob under gravity"""
+    sources (kernel logic + the whole C++ host layer): Bob under gravity, and
+    the inverse problem with its round trip"""
     lib_dir = tmp_path / "lib"
     lib_dir.mkdir()
     src = os.path.join(ROOT, "tests", "_hostemu", "libsanm_b200_hostemu.so")
     os.symlink(src, lib_dir / "libsanm_b200.so")
-    check_pair("bob", tmp_path, str(lib_dir))
+    check_pair(name, tmp_path, str(lib_dir))
 
 
 @pytest.mark.gpu
