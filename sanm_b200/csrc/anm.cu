@@ -1,5 +1,6 @@
 /* sanm_b200/csrc/anm.cu -- see anm.h. */
 #include "anm.h"
+#include "pade_dev.h"
 #include "cache.h"
 #include "comm.h"
 #include "shard.h"
@@ -444,8 +445,15 @@ std::vector<const double*> AnmSolver::coeff_ptrs() const {
     return p;
 }
 
+void AnmSolver::ensure_host_series() const {
+    if (m_h_xt_valid) return;
+    rt::d2h(m_h_xt.data(), m_d_xt.ptr(), m_nr_coeffs * m_ld * sizeof(double));
+    m_h_xt_valid = true;
+}
+
 const double* AnmSolver::xt_coeff(size_t i) const {
     sanm_check(i < m_nr_coeffs);
+    ensure_host_series();
     return m_h_xt.data() + i * m_ld;
 }
 
@@ -512,6 +520,7 @@ void AnmSolver::solve_expansion_coeffs() {
     std::memcpy(m_h_xt.data(), m_xt0.data(), (n + 1) * sizeof(double));
     rt::h2d(m_d_xt.ptr(), m_xt0.data(), (n + 1) * sizeof(double));
     m_nr_coeffs = 1;
+    m_h_xt_valid = true;
 
     const Shape elem_shape = m_rin_e->out_shape();
     m_prop->prepare(elem_shape);
@@ -679,15 +688,35 @@ void AnmSolver::solve_expansion_coeffs() {
     }
     m_stats.tet_order_steps += (double)m_prop->batch() * K;
 
-    // one copy of the whole series to the host, then the scalar decisions
-    rt::d2h(m_h_xt.data(), m_d_xt.ptr(), (size_t)(K + 1) * m_ld * sizeof(double));
+    // The series stays on the device: its norms, t coefficients
+    // and a finiteness flag are reduced there, and the Pade passes read it in
+    // place (pade_dev.cu).  SANM_HOST_PADE=1: one copy of the whole series to
+    // the host and the host passes of pade.cpp instead.
     m_nr_coeffs = K + 1;
+    m_h_xt_valid = false;
     m_prop->check_device_error();
-    for (size_t i = 0; i < m_h_xt.size(); i += m_ld) {
-        for (uint64_t j = 0; j <= n; ++j) {
-            sanm_check(std::isfinite(m_h_xt[i + j]),
-                       "non-finite value in series coefficient %zu",
-                       (size_t)(i / m_ld));
+    m_series_on_device = getenv("SANM_HOST_PADE") == nullptr &&
+                         device_pade_supported(K + 1);
+    if (m_series_on_device) {
+        SANM_PROF("series_summary");
+        int bad = -1;
+        series_dev::summary(m_d_xt.ptr(), K + 1, m_ld, n + 1, m_norm2, m_t_coeffs,
+                            &bad);
+        sanm_check(bad < 0, "non-finite value in series coefficient %d", bad);
+    } else {
+        ensure_host_series();
+        m_norm2.assign(K + 1, 0.0);
+        m_t_coeffs.resize(K + 1);
+        for (int i = 0; i <= K; ++i) {
+            const double* p = m_h_xt.data() + (size_t)i * m_ld;
+            double s2 = 0;
+            for (uint64_t j = 0; j <= n; ++j) {
+                sanm_check(std::isfinite(p[j]),
+                           "non-finite value in series coefficient %d", i);
+                s2 += p[j] * p[j];
+            }
+            m_norm2[i] = s2;
+            m_t_coeffs[i] = p[n];
         }
     }
     if (m_hyper.sanity_check && !m_hyper.xcoeff_l2_penalty) {
@@ -711,12 +740,7 @@ void AnmSolver::solve_expansion_coeffs() {
         // same trace as libsanm/anm.cpp:295-309
         printf("\nbound=%g t=%g\n", m_t_max_a, m_t_max);
         printf("x(a):");
-        for (int i = 0; i <= K; ++i) {
-            double s2 = 0;
-            const double* p = m_h_xt.data() + (size_t)i * m_ld;
-            for (uint64_t j = 0; j <= n; ++j) s2 += p[j] * p[j];
-            printf(" %.3g", std::sqrt(s2));
-        }
+        for (int i = 0; i <= K; ++i) printf(" %.3g", std::sqrt(m_norm2[i]));
         printf("\nt(a):");
         for (double t : m_t_coeffs) printf(" %.3g,", t);
         printf("\n");
@@ -729,18 +753,11 @@ void AnmSolver::estimate_valid_range() {
     // libsanm/anm.cpp:117-154
     const int K = m_hyper.order;
     const uint64_t len = m_n + 1;
-    auto norm = [&](size_t i) {
-        const double* p = m_h_xt.data() + i * m_ld;
-        double s = 0;
-        for (uint64_t j = 0; j < len; ++j) s += p[j] * p[j];
-        return std::sqrt(s);
-    };
+    auto norm = [&](size_t i) { return std::sqrt(m_norm2[i]); };
     double x1 = norm(1), xback = std::max(norm(K), 1e-15);
     double a_bound = std::pow(m_hyper.maxr / xback * x1, 1.0 / double(K - 1));
     a_bound = std::min(a_bound, m_max_a_bound);
-    m_t_coeffs.resize(K + 1);
-    for (int i = 0; i <= K; ++i) m_t_coeffs[i] = m_h_xt[(size_t)i * m_ld + m_n];
-    sanm_check(m_t_coeffs[1] > 0);
+    sanm_check((int)m_t_coeffs.size() == K + 1 && m_t_coeffs[1] > 0);
     m_t_max_a = a_bound;
     m_a_bound_taylor = a_bound;
     m_t_max = poly::eval(m_t_coeffs, a_bound);
@@ -750,8 +767,14 @@ void AnmSolver::estimate_valid_range() {
     static const bool env_pade = getenv("SANM_PADE") != nullptr;
     if ((m_hyper.use_pade || env_pade) && a_bound < m_max_a_bound) {
         SANM_PROF("pade");
-        m_pade.reset(new PadeApproximation{coeff_ptrs(), len,
-                                           !m_hyper.xcoeff_l2_penalty, false});
+        if (m_series_on_device) {
+            m_pade.reset(new PadeApproximation{
+                    make_device_pade_ops(m_d_xt.ptr(), K + 1, m_ld, len),
+                    !m_hyper.xcoeff_l2_penalty, false});
+        } else {
+            m_pade.reset(new PadeApproximation{coeff_ptrs(), len,
+                                               !m_hyper.xcoeff_l2_penalty, false});
+        }
         if (m_pade->estimate_valid_range(a_bound, m_hyper.maxr, m_max_a_bound)) {
             m_t_max_a = m_pade->get_t_max_a();
             m_t_max = m_pade->get_t_max();
@@ -766,6 +789,12 @@ std::vector<double> AnmSolver::eval_xt(double a) const {
     if (m_pade) return m_pade->eval_xt(a);
     const uint64_t len = m_n + 1;
     sanm_check(m_nr_coeffs >= 1);
+    if (m_series_on_device && m_nr_coeffs > 1 && !m_h_xt_valid) {
+        std::vector<double> ret(len);
+        series_dev::horner(m_d_xt.ptr(), m_nr_coeffs, m_ld, len, a, ret.data());
+        return ret;
+    }
+    ensure_host_series();
     std::vector<double> ret(m_h_xt.begin() + (m_nr_coeffs - 1) * m_ld,
                             m_h_xt.begin() + (m_nr_coeffs - 1) * m_ld + len);
     for (size_t i = m_nr_coeffs - 1; i-- > 0;) {
@@ -792,6 +821,9 @@ void AnmSolver::update_approx() {
     // (libsanm/anm.cpp:118-122).  Every recovery is counted
     // (sanm_anm_robustness_stats) so that such a run cannot pass for a clean one.
     const bool recover = getenv("SANM_PADE_RECOVER") != nullptr;  // once per ANM iteration
+    // (the retry re-evaluates the OLD series, which the failed expansion
+    // overwrites on the device: keep its host copy)
+    if (recover) ensure_host_series();
 #ifdef SANM_HOSTEMU
     // test-only (host-emulation build): take the recovery path once without a
     // failing check

@@ -169,7 +169,12 @@ private:
 
     // host state
     std::vector<double> m_xt0;          //!< [n + 1]
-    std::vector<double> m_h_xt;         //!< (order+1) x ld series, host copy
+    //! (order+1) x ld series, host copy: filled on demand (xt_coeff(), verbose
+    //! trace, recovery), the series itself lives in m_d_xt
+    mutable std::vector<double> m_h_xt;
+    mutable bool m_h_xt_valid = false;
+    bool m_series_on_device = false;
+    std::vector<double> m_norm2;        //!< squared norms of the series vectors
     std::vector<double> m_t_coeffs;
     std::vector<double> m_v_host;       //!< VECSCALE: v ; EQN: y
     std::vector<double> m_fx0_host;     //!< IMPLICIT: f(x0, t0)
@@ -204,6 +209,7 @@ private:
     std::vector<double> eval_xt(double a) const;
     double t0() const { return m_t_coeffs[0]; }
     std::vector<const double*> coeff_ptrs() const;
+    void ensure_host_series() const;
     void dot_to(int slot, const double* a, const double* b, uint64_t n);
 };
 

@@ -11,9 +11,10 @@
 namespace sanm_b200 {
 
 namespace {
+constexpr size_t CHUNK = 4096;
+
 //! fixed chunking => the result does not depend on the number of threads
 double dot(const double* a, const double* b, size_t n) {
-    constexpr size_t CHUNK = 4096;
     const size_t nchunk = (n + CHUNK - 1) / CHUNK;
     if (nchunk <= 1) {
         double s = 0;
@@ -32,167 +33,92 @@ double dot(const double* a, const double* b, size_t n) {
     for (double v : part) s += v;
     return s;
 }
-}  // namespace
 
-PadeApproximation::PadeApproximation(std::vector<const double*> xs, size_t len,
-                                     bool anm_cond, bool sanity_check)
-        : m_sanity_check{sanity_check}, m_xs{std::move(xs)}, m_len{len} {
-    const size_t nx = m_xs.size();
-    sanm_check(nx >= 3);
-    if (len < nx * 2 || nx <= 4) return;  // pade.cpp:19-21
-    std::vector<double> astore(nx * nx, 0.0);
-    auto a = [&](int i, int j) -> double& { return astore[i * nx + j]; };
-    const int n = (int)nx - 1;
-    constexpr double eps = std::numeric_limits<double>::epsilon();
+class HostPadeOps final : public PadeVectorOps {
+    std::vector<const double*> m_xs;
+    size_t m_len;
 
-    // modified Gram-Schmidt of x_1..x_n (pade.cpp:30-55)
-    std::vector<std::vector<double>> orth(nx);
-    // Per i: all projections a(i, j) in ONE pass over x_i (they use the
-    // original x_i, so they do not depend on each other), then one pass that
-    // subtracts them in the order j = 1, 2, ...  Chunking and summation orders
-    // are those of dot() above, so the numbers are the ones of the plain
-    // j-by-j loop; only the number of parallel regions drops from O(n^2) to
-    // O(n) (they cost more than the arithmetic on a 22 k-vector).
-    constexpr size_t CHUNK = 4096;
-    const size_t nchunk = (len + CHUNK - 1) / CHUNK;
-    const bool par = nchunk > 1;
-    std::vector<double> part((size_t)nx * std::max<size_t>(nchunk, 1));
-    for (int i = 1; i <= n; ++i) {
-        auto& u = orth[i];
-        u.assign(m_xs[i], m_xs[i] + len);
-        if (i > 1) {
-            const double* xi = m_xs[i];
+public:
+    HostPadeOps(std::vector<const double*> xs, size_t len)
+            : m_xs{std::move(xs)}, m_len{len} {}
+    size_t nx() const override { return m_xs.size(); }
+    size_t len() const override { return m_len; }
+    double t_coeff(size_t i) const override { return m_xs[i][m_len - 1]; }
+
+    bool gram_schmidt(bool anm_cond, double* astore) override {
+        const size_t nx = m_xs.size(), len = m_len;
+        auto a = [&](int i, int j) -> double& { return astore[i * nx + j]; };
+        const int n = (int)nx - 1;
+        constexpr double eps = std::numeric_limits<double>::epsilon();
+        std::vector<std::vector<double>> orth(nx);
+        // Per i: all projections a(i, j) in ONE pass over x_i (they use the
+        // original x_i, so they do not depend on each other), then one pass
+        // that subtracts them in the order j = 1, 2, ...  Chunking and
+        // summation orders are those of dot() above, so the numbers are the
+        // ones of the plain j-by-j loop; only the number of parallel regions
+        // drops from O(n^2) to O(n).
+        const size_t nchunk = (len + CHUNK - 1) / CHUNK;
+        const bool par = nchunk > 1;
+        std::vector<double> part((size_t)nx * std::max<size_t>(nchunk, 1));
+        for (int i = 1; i <= n; ++i) {
+            auto& u = orth[i];
+            u.assign(m_xs[i], m_xs[i] + len);
+            if (i > 1) {
+                const double* xi = m_xs[i];
 #pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (par)
-            for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
-                const size_t i0 = c * CHUNK, i1 = std::min(len, i0 + CHUNK);
+                for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
+                    const size_t i0 = c * CHUNK, i1 = std::min(len, i0 + CHUNK);
+                    for (int j = 1; j < i; ++j) {
+                        const double* o = orth[j].data();
+                        double sacc = 0;
+                        for (size_t q = i0; q < i1; ++q) sacc += xi[q] * o[q];
+                        part[(size_t)j * nchunk + c] = sacc;
+                    }
+                }
+                std::vector<double> fac(i, 0.0);
                 for (int j = 1; j < i; ++j) {
-                    const double* o = orth[j].data();
                     double sacc = 0;
-                    for (size_t q = i0; q < i1; ++q) sacc += xi[q] * o[q];
-                    part[(size_t)j * nchunk + c] = sacc;
+                    for (size_t c = 0; c < nchunk; ++c) sacc += part[(size_t)j * nchunk + c];
+                    a(i, j) = sacc;
+                    if (anm_cond && j == 1) {
+                        sanm_check(std::fabs(a(i, j)) < 1e-4);
+                        a(i, j) = 0;
+                    } else {
+                        fac[j] = -a(i, j);
+                    }
                 }
-            }
-            std::vector<double> fac(i, 0.0);
-            for (int j = 1; j < i; ++j) {
-                double sacc = 0;
-                for (size_t c = 0; c < nchunk; ++c) sacc += part[(size_t)j * nchunk + c];
-                a(i, j) = sacc;
-                if (anm_cond && j == 1) {
-                    sanm_check(std::fabs(a(i, j)) < 1e-4);
-                    a(i, j) = 0;
-                } else {
-                    fac[j] = -a(i, j);
-                }
-            }
-            const int j_first = anm_cond ? 2 : 1;
+                const int j_first = anm_cond ? 2 : 1;
 #pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (par)
-            for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
-                const size_t i0 = c * CHUNK, i1 = std::min(len, i0 + CHUNK);
-                for (int j = j_first; j < i; ++j) {
-                    const double* o = orth[j].data();
-                    const double f = fac[j];
-                    for (size_t q = i0; q < i1; ++q) u[q] += o[q] * f;
+                for (int64_t c = 0; c < (int64_t)nchunk; ++c) {
+                    const size_t i0 = c * CHUNK, i1 = std::min(len, i0 + CHUNK);
+                    for (int j = j_first; j < i; ++j) {
+                        const double* o = orth[j].data();
+                        const double f = fac[j];
+                        for (size_t q = i0; q < i1; ++q) u[q] += o[q] * f;
+                    }
                 }
             }
-        }
-        double aii = std::sqrt(dot(u.data(), u.data(), len));
-        if (aii == 0) {
-            m_d.clear();
-            return;
-        }
-        a(i, i) = aii;
-        double inv = 1 / std::max(aii, eps);
-        for (auto& v : u) v *= inv;
-        if (aii < eps) {
-            double nn = 1 / std::sqrt(dot(u.data(), u.data(), len));
-            for (auto& v : u) v *= nn;
-        }
-    }
-
-    auto solve_d = [&](std::vector<double>& d, int nn) {
-        // pade.cpp:68-92
-        d.assign(nn, 0.0);
-        d[0] = 1;
-        for (int i = 1; i < nn; ++i) {
-            double s = 0;
-            for (int j = 0; j < i; ++j) s += a(nn - j, nn - i) * d[j];
-            double y = a(nn - i, nn - i);
-            d[i] = -s * y / (y * y + 1e-20);
-        }
-        if (m_sanity_check) {
-            for (int i = 1; i < nn; ++i) {
-                double s = 0;
-                for (int j = 0; j <= nn - i; ++j) s += a(nn - j, i) * d[j];
-                sanm_check(std::fabs(s) < 1e-5, "%g", s);
+            double aii = std::sqrt(dot(u.data(), u.data(), len));
+            if (aii == 0) return false;
+            a(i, i) = aii;
+            double inv = 1 / std::max(aii, eps);
+            for (auto& v : u) v *= inv;
+            if (aii < eps) {
+                double nn = 1 / std::sqrt(dot(u.data(), u.data(), len));
+                for (auto& v : u) v *= nn;
             }
         }
-    };
-    solve_d(m_d, n);
-    solve_d(m_d_lo, n - 1);
-
-    m_t_nume_coeffs.assign(n, 0.0);
-    for (int i = 0; i < n; ++i) {
-        double ti = m_xs[i][len - 1];
-        if (!i) {
-            m_t0 = ti;
-        } else {
-            for (int j = 0; j < n - i; ++j) m_t_nume_coeffs[i + j] += m_d[j] * ti;
-        }
+        return true;
     }
-}
 
-std::vector<double> PadeApproximation::eval_nume(double a, const double* d,
-                                                 int n) const {
-    // pade.cpp:187-194
-    std::vector<double> sum(m_len, 0.0), scale(n + 1, 0.0);
-    for (int i = n; i >= 1; --i) scale[i] = poly::eval(d, n - i + 1, a);
-    constexpr int64_t CHUNK = 4096;
-    const int64_t nchunk = ((int64_t)m_len + CHUNK - 1) / CHUNK;
-#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (nchunk > 1)
-    for (int64_t c = 0; c < nchunk; ++c) {
-        const int64_t q0 = c * CHUNK, q1 = std::min<int64_t>(m_len, q0 + CHUNK);
-        // Horner per element, i = n .. 1 (same operation order as a pass per i)
-        for (int i = n; i >= 1; --i) {
-            const double* x = m_xs[i];
-            const double sc = scale[i];
-            for (int64_t q = q0; q < q1; ++q) sum[q] = sum[q] * a + x[q] * sc;
-        }
-    }
-    return sum;
-}
-
-double PadeApproximation::eval_t(double a) const {
-    return poly::eval(m_t_nume_coeffs, a) / poly::eval(m_d, a) + m_t0;
-}
-
-bool PadeApproximation::estimate_valid_range(double start, double eps,
-                                             double limit) {
-    sanm_check(start > 0 && eps > 0);
-    if (m_d.empty()) return false;
-    std::vector<std::complex<double>> rts;
-    if (!poly::roots(m_d, true, rts)) return false;
-    double pole = 0;
-    for (auto& r : rts) {
-        sanm_check(r.imag() == 0);
-        if (r.real() > 0 && (pole == 0 || r.real() < pole)) pole = r.real();
-    }
-    if (pole == 0) pole = start * 4;
-    if (pole <= start) return false;
-
-    const double eps2 = eps * eps;
-    const int n = (int)m_xs.size() - 2;
-    // One fused pass per candidate: both numerators by Horner (x_i read once
-    // for the two), their weighted difference and the two squared norms.  The
-    // element operations and the chunked summation are those of eval_nume() +
-    // dot(), so the decision is the one of the unfused form.
-    constexpr int64_t CHUNK = 4096;
-    const int64_t nchunk = ((int64_t)m_len + CHUNK - 1) / CHUNK;
-    std::vector<double> part_d(nchunk), part_n(nchunk), sc_n(n + 1), sc_l(n + 1);
-    auto check = [&](double a) {
-        double denom_n = poly::eval(m_d, a), denom_lo = poly::eval(m_d_lo, a);
-        const double f = denom_n / denom_lo;
-        for (int i = n; i >= 1; --i) sc_n[i] = poly::eval(m_d.data(), n - i + 1, a);
-        for (int i = n - 1; i >= 1; --i) sc_l[i] = poly::eval(m_d_lo.data(), n - 1 - i + 1, a);
+    void check_norms(double a, const double* sc_n, const double* sc_l, int n,
+                     double f, double* diff2_out, double* pn2_out) const override {
+        // One fused pass per candidate: both numerators by Horner (x_i read
+        // once for the two), their weighted difference and the two squared
+        // norms.  The element operations and the chunked summation are those
+        // of the unfused form (eval_nume + dot).
+        const int64_t nchunk = ((int64_t)m_len + CHUNK - 1) / CHUNK;
+        std::vector<double> part_d(nchunk), part_n(nchunk);
 #pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (nchunk > 1)
         for (int64_t c = 0; c < nchunk; ++c) {
             const int64_t q0 = c * CHUNK, q1 = std::min<int64_t>(m_len, q0 + CHUNK);
@@ -224,6 +150,110 @@ bool PadeApproximation::estimate_valid_range(double start, double eps,
             diff2 += part_d[c];
             pn2 += part_n[c];
         }
+        *diff2_out = diff2;
+        *pn2_out = pn2;
+    }
+
+    void eval_xt(double a, const double* sc, int n, double f,
+                 double* out) const override {
+        // pade.cpp:181-194, 219-224
+        const int64_t nchunk = ((int64_t)m_len + CHUNK - 1) / CHUNK;
+#pragma omp parallel for num_threads(::sanm_b200::rt::host_threads()) schedule(static) if (nchunk > 1)
+        for (int64_t c = 0; c < nchunk; ++c) {
+            const int64_t q0 = c * CHUNK, q1 = std::min<int64_t>(m_len, q0 + CHUNK);
+            for (int64_t q = q0; q < q1; ++q) out[q] = 0.0;
+            // Horner per element, i = n .. 1 (same operation order as a pass per i)
+            for (int i = n; i >= 1; --i) {
+                const double* x = m_xs[i];
+                const double s = sc[i];
+                for (int64_t q = q0; q < q1; ++q) out[q] = out[q] * a + x[q] * s;
+            }
+            for (int64_t q = q0; q < q1; ++q) out[q] = out[q] * f + m_xs[0][q];
+        }
+    }
+};
+}  // namespace
+
+std::unique_ptr<PadeVectorOps> make_host_pade_ops(std::vector<const double*> xs,
+                                                  size_t len) {
+    return std::make_unique<HostPadeOps>(std::move(xs), len);
+}
+
+PadeApproximation::PadeApproximation(std::unique_ptr<PadeVectorOps> ops,
+                                     bool anm_cond, bool sanity_check)
+        : m_sanity_check{sanity_check}, m_ops{std::move(ops)} {
+    const size_t nx = m_ops->nx(), len = m_ops->len();
+    sanm_check(nx >= 3);
+    if (len < nx * 2 || nx <= 4) return;  // pade.cpp:19-21
+    std::vector<double> astore(nx * nx, 0.0);
+    auto a = [&](int i, int j) -> double& { return astore[i * nx + j]; };
+    const int n = (int)nx - 1;
+    if (!m_ops->gram_schmidt(anm_cond, astore.data())) {
+        m_d.clear();
+        return;
+    }
+
+    auto solve_d = [&](std::vector<double>& d, int nn) {
+        // pade.cpp:68-92
+        d.assign(nn, 0.0);
+        d[0] = 1;
+        for (int i = 1; i < nn; ++i) {
+            double s = 0;
+            for (int j = 0; j < i; ++j) s += a(nn - j, nn - i) * d[j];
+            double y = a(nn - i, nn - i);
+            d[i] = -s * y / (y * y + 1e-20);
+        }
+        if (m_sanity_check) {
+            for (int i = 1; i < nn; ++i) {
+                double s = 0;
+                for (int j = 0; j <= nn - i; ++j) s += a(nn - j, i) * d[j];
+                sanm_check(std::fabs(s) < 1e-5, "%g", s);
+            }
+        }
+    };
+    solve_d(m_d, n);
+    solve_d(m_d_lo, n - 1);
+
+    m_t_nume_coeffs.assign(n, 0.0);
+    for (int i = 0; i < n; ++i) {
+        double ti = m_ops->t_coeff(i);
+        if (!i) {
+            m_t0 = ti;
+        } else {
+            for (int j = 0; j < n - i; ++j) m_t_nume_coeffs[i + j] += m_d[j] * ti;
+        }
+    }
+}
+
+double PadeApproximation::eval_t(double a) const {
+    return poly::eval(m_t_nume_coeffs, a) / poly::eval(m_d, a) + m_t0;
+}
+
+bool PadeApproximation::estimate_valid_range(double start, double eps,
+                                             double limit) {
+    sanm_check(start > 0 && eps > 0);
+    if (m_d.empty()) return false;
+    std::vector<std::complex<double>> rts;
+    if (!poly::roots(m_d, true, rts)) return false;
+    double pole = 0;
+    for (auto& r : rts) {
+        sanm_check(r.imag() == 0);
+        if (r.real() > 0 && (pole == 0 || r.real() < pole)) pole = r.real();
+    }
+    if (pole == 0) pole = start * 4;
+    if (pole <= start) return false;
+
+    const double eps2 = eps * eps;
+    const int n = (int)m_ops->nx() - 2;
+    std::vector<double> sc_n(n + 1), sc_l(n + 1);
+    auto check = [&](double a) {
+        // pade.cpp:137-147
+        double denom_n = poly::eval(m_d, a), denom_lo = poly::eval(m_d_lo, a);
+        const double f = denom_n / denom_lo;
+        for (int i = n; i >= 1; --i) sc_n[i] = poly::eval(m_d.data(), n - i + 1, a);
+        for (int i = n - 1; i >= 1; --i) sc_l[i] = poly::eval(m_d_lo.data(), n - 1 - i + 1, a);
+        double diff2 = 0, pn2 = 0;
+        m_ops->check_norms(a, sc_n.data(), sc_l.data(), n, f, &diff2, &pn2);
         return diff2 <= pn2 * eps2;
     };
     double left = start * 1.001, right = start + (pole - start) * 0.99;
@@ -260,9 +290,10 @@ double PadeApproximation::solve_a(double t) const {
 }
 
 std::vector<double> PadeApproximation::eval_xt(double a) const {
-    std::vector<double> ret = eval_nume(a, m_d.data(), (int)m_xs.size() - 2);
-    const double f = a / poly::eval(m_d, a);
-    for (size_t q = 0; q < m_len; ++q) ret[q] = ret[q] * f + m_xs[0][q];
+    const int n = (int)m_ops->nx() - 2;
+    std::vector<double> sc(n + 1, 0.0), ret(m_ops->len());
+    for (int i = n; i >= 1; --i) sc[i] = poly::eval(m_d.data(), n - i + 1, a);
+    m_ops->eval_xt(a, sc.data(), n, a / poly::eval(m_d, a), ret.data());
     return ret;
 }
 
