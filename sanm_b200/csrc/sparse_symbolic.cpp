@@ -766,20 +766,54 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
     // ---- column counts of L (off-diagonal) by row-subtree traversal
     std::vector<u32> cc(n, 0);
     {
-        std::vector<u32> mark(n, ~0u);
+        // On the supervariable graph: the members of a supervariable are
+        // adjacent in the (post)order and form a chain of the elimination
+        // tree, so column t of a supervariable s of weight w has
+        //   cc = (w - 1 - t) + sum of the weights of the later supervariables
+        //        in the column structure of s,
+        // and the row-subtree traversal runs over |L| / w^2 entries (3 unknowns
+        // per mesh vertex: 9 times fewer; 2.2 s -> 0.25 s for a 1 M-tet cube).
+        std::vector<u32> cidx(nsv, ~0u), cfirst, clast;  // order of the supervariables
         for (u32 i = 0; i < n; ++i) {
+            const u32 s = sv[perm[i]];
+            if (cidx[s] == ~0u) {
+                cidx[s] = (u32)cfirst.size();
+                cfirst.push_back(i);
+                clast.push_back(i);
+            } else {
+                // members must be contiguous
+                sanm_check(clast[cidx[s]] + 1 == i, "supervariable split by the ordering");
+                clast[cidx[s]] = i;
+            }
+        }
+        const u32 m = (u32)cfirst.size();
+        std::vector<u32> sv_at(m);  // supervariable at compressed position
+        for (u32 s = 0; s < nsv; ++s) sv_at[cidx[s]] = s;
+        std::vector<int32_t> cparent(m, -1);
+        for (u32 c = 0; c < m; ++c) {
+            const int32_t pl = parent[clast[c]];
+            if (pl >= 0) cparent[c] = (int32_t)cidx[sv[perm[pl]]];
+        }
+        std::vector<u64> ccs(m, 0);
+        std::vector<u32> mark(m, ~0u);
+        for (u32 i = 0; i < m; ++i) {
             mark[i] = i;
-            u32 oi = perm[i];
-            for (auto p = adj.begin(oi); p != adj.end(oi); ++p) {
-                u32 k = iperm[*p];
+            const u32 si = sv_at[i];
+            const u64 wi = weight[si];
+            for (auto p = cg.begin(si); p != cg.end(si); ++p) {
+                const u32 k = cidx[*p];
                 if (k >= i) continue;
                 u32 j = k;
                 while (mark[j] != i) {
-                    ++cc[j];
+                    ccs[j] += wi;
                     mark[j] = i;
-                    j = (u32)parent[j];
+                    j = (u32)cparent[j];
                 }
             }
+        }
+        for (u32 c = 0; c < m; ++c) {
+            const u32 w = clast[c] - cfirst[c] + 1;
+            for (u32 t = 0; t < w; ++t) cc[cfirst[c] + t] = (u32)((w - 1 - t) + ccs[c]);
         }
     }
 
