@@ -11,6 +11,7 @@
 #endif
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 
 namespace sanm_b200 {
@@ -903,6 +904,17 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                        const uint32_t* colidx, const double* node_keys) {
     rt::check_device();
     sanm_check(n > 0 && n < (1ull << 31));
+    // SANM_LU_DEBUG: host wall time of the stages of this call
+    const bool dbg = getenv("SANM_LU_DEBUG") != nullptr;
+    auto lap_t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!dbg) return;
+        rt::sync();
+        auto t1 = std::chrono::steady_clock::now();
+        printf("[lu-setup] %-34s %8.2f ms\n", what,
+               std::chrono::duration<double, std::milli>(t1 - lap_t0).count());
+        lap_t0 = t1;
+    };
     Impl& I = *m_impl;
     m_n = n;
     m_nnz = rowptr[n];
@@ -933,6 +945,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     }
     LuTopo& T = *I.topo;
     const Symbolic& S = *T.sym;
+    lap(fresh ? "pattern hash + symbolic analysis" : "pattern hash + cache hit");
 
     if (fresh) {
         T.rowptr.upload(T.h_rowptr);
@@ -953,6 +966,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     I.scal.alloc(4 + ABSMAX_BLOCKS);
     I.counters.alloc(4);
     I.counters.zero();
+    lap("uploads + numeric buffers");
 
     // flattened gather lists of the forward sweep: for row i of front s the
     // positions (in the work-vector array) of the children's update entries
@@ -1001,6 +1015,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                "front of %u rows: the assembly kernel indexes a front with 32 bits",
                max_front);
     I.fd.upload(fd);
+    lap("gather lists + front descriptors");
 
     const uint32_t nlev = (uint32_t)S.level_ptr.size() - 1;
     if (fresh) {
@@ -1087,6 +1102,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
     if (prep_t.empty()) prep_t.push_back({0, 0});
     T.prep_tasks.upload(prep_t);
     }  // fresh
+    lap("level task lists");
 
     if (getenv("SANM_LU_DEBUG")) {
         printf("[lu] n=%zu nnz=%zu nsn=%u levels=%u factor_entries=%zu "
