@@ -267,12 +267,20 @@ KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
     uint64_t key = m_rin->hash_struct() * 0x9E3779B97F4A7C15ull ^
                    m_rout->hash_struct();
     key = hash_bytes(&key, 8, n * 131 + odim * 17 + idim * 3 + elemwise);
-    m_pat = cache.get(key);
-    if (m_pat && m_pat->rowptr.size() == n + 1) return;
     const auto& orp = m_rout->h_rowptr();
     const auto& oix = m_rout->h_idx();
     const auto& irp = m_rin->h_rowptr();
     const auto& iix = m_rin->h_idx();
+    // independent witness of the inputs: sizes + 128 strided samples per array
+    std::vector<uint64_t> witness{n, (uint64_t)odim, (uint64_t)idim,
+                                  (uint64_t)elemwise, orp.size(), oix.size(),
+                                  irp.size(), iix.size()};
+    for (const auto* v : {&orp, &oix, &irp, &iix}) {
+        const size_t step = std::max<size_t>(1, v->size() / 128);
+        for (size_t q = 0; q < v->size(); q += step) witness.push_back((*v)[q]);
+    }
+    m_pat = cache.get(key);
+    if (m_pat && m_pat->rowptr.size() == n + 1 && m_pat->witness == witness) return;
     // structural pattern (independent of values): for every output row the
     // union, over the items it touches, of the unknowns those items read
     std::vector<std::vector<uint32_t>> rows(n);
@@ -326,6 +334,7 @@ KAssembler::KAssembler(std::shared_ptr<const Remap> rin,
     pat->d_colidx.upload(m_colidx);
     pat->hash = hash_vec(m_colidx, hash_vec(m_rowptr, n));
     m_pat = pat;
+    pat->witness = std::move(witness);
     cache.put(key, m_pat);
 }
 
@@ -606,6 +615,9 @@ void AnmSolver::solve_expansion_coeffs() {
                                        m_kasm->pattern_hash();
                         key = hash_bytes(&key, 8, n);
                         m_kfused = io.hash ? kcache.get(key) : nullptr;
+                        if (m_kfused && !m_kfused->matches(io.n_tets, n, m_kasm->nnz())) {
+                            m_kfused.reset();  // hash collision
+                        }
                         if (!m_kfused) {
                             m_kfused = FusedKAssembly::build(
                                     io, n, m_kasm->rowptr(), m_kasm->colidx());

@@ -58,6 +58,10 @@ public:
         std::vector<uint32_t> rowptr, colidx;
         rt::DBuf<uint32_t> d_rowptr, d_colidx;
         uint64_t hash = 0;
+        //! sizes and strided samples of the two maps the pattern was built
+        //! from: a cache hit is accepted only if they agree (a 64-bit hash
+        //! alone is not proof)
+        std::vector<uint64_t> witness;
     };
     //! vals (device, nnz) and grad_t (device, n; may be null) from the
     //! per-item Jacobian (device, [N][odim][idim] or [N][dim]; with
@@ -87,6 +91,10 @@ public:
     //! jac: [81][jac_pitch] (TaylorProp::ensure_jacobian of a fused graph)
     void assemble(double* vals, double* grad_t, const double* jac,
                   int64_t jac_pitch, const FusedIO& io) const;
+    //! the sizes this object was built for (checked on a cache hit)
+    bool matches(uint64_t n_tets, uint64_t n, uint64_t nnz) const {
+        return m_n_tets == n_tets && m_n == n && m_nnz == nnz;
+    }
 
 private:
     FusedKAssembly() = default;

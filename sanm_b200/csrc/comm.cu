@@ -90,6 +90,23 @@ void halo_setup(Halo& h, uint64_t lo, uint64_t hi, uint64_t n) {
             h.peers.push_back({q, olo, ohi - olo, off});
             off += ohi - olo;
         }
+        // The sum of a shared row is formed pairwise with the neighbour (lower
+        // rank first), which is the same on both owners only if a row has at
+        // most two of them: true for slabs at least two vertex planes thick.
+        // Refuse anything else rather than break the bitwise-identical-owners
+        // guarantee.
+        for (size_t a = 0; a < h.peers.size(); ++a) {
+            for (size_t c = a + 1; c < h.peers.size(); ++c) {
+                const auto &pa = h.peers[a], &pc = h.peers[c];
+                sanm_check(pa.lo + pa.cnt <= pc.lo || pc.lo + pc.cnt <= pa.lo,
+                           "halo exchange: rows [%zu, %zu) are shared by more than "
+                           "two ranks (%d, %d and this one); use the all-reduce "
+                           "exchange for this partition",
+                           (size_t)std::max(pa.lo, pc.lo),
+                           (size_t)std::min(pa.lo + pa.cnt, pc.lo + pc.cnt), pa.rank,
+                           pc.rank);
+            }
+        }
         h.scratch.alloc(off ? off : 1);
     }
 #endif

@@ -251,3 +251,14 @@ def test_tangent_matrix_by_value(impl, ref, energy, driver):
     assert abs(Ka - Kr).max() <= 1e-10 * scale
     # what the reference dropped really is below its threshold here
     assert Kr.nnz <= Ka.nnz
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("energy", [mat.NEOHOOKEAN_C, mat.NEOHOOKEAN_I,
+                                    mat.ARAP])
+def test_sweep_large_gpu(cuda_impl, ref, energy):
+    """121,500 tets (950 tiles: several waves of blocks on 148 SMs), 89 k
+    output rows (beyond 16-bit row ids, many partials per row), order 8,
+    against the oracle's sweep -- the sizes of the other parity tests (<= 360
+    tets) never leave one wave.  GPU only: the oracle needs ~10 s per energy."""
+    check_sweep(cuda_impl, ref, (46, 31, 19), energy, 8)
