@@ -360,7 +360,8 @@ def sparse_summary(es):
           "factor_ms_total": e["factor_ms"], "nr_factor": e["nr_factor"],
           "solve_ms_total": e["solve_ms"], "nr_solves": e["nr_solves"],
           "element_ms_total": e["element_ms"],
-          "pade_recovered": e.get("pade_recovered"),
+          # (counted per solver object: summed over the run's solvers)
+          "pade_recovered": sum(x.get("pade_recovered") or 0 for x in es),
           "lu_perturbed_pivots": e.get("lu_perturbed_pivots"),
           "lu_refine_steps": e.get("lu_refine_steps")}
     if e["nr_solves"] and e["solve_ms"] > 0:
