@@ -506,11 +506,14 @@ void FusedProp::launch_step(int k_push, int kb, bool want_out, const double* x) 
         // register file allows; __launch_bounds__(128, 1) (255 registers) gives
         // 1.76 G tet*order/s where (128, 5) gives 2.49 G
 #ifndef SANM_HOSTEMU
-        // steady-state step of a sweep: slots staged by bulk copies
-        // (StepKernelBulk above); SANM_STEP_BULK=0 keeps the register-staged form
+        // SANM_STEP_BULK=1: slots staged by bulk copies (StepKernelBulk above).
+        // Opt-in: measured SLOWER than the register-staged kernel on the B200
+        // (2 M tets, K = 20: NH-C 1.95 vs 2.50 G tet*order/s, ARAP 1.47 vs 1.57)
+        // -- two blocks per SM leave the SM idle during each block's gather /
+        // assembly phases and keep only ~2 slots per block in flight.
         static const bool bulk = [] {
             const char* e = getenv("SANM_STEP_BULK");
-            return !(e && e[0] == '0');
+            return e && e[0] == '1';
         }();
         if (use_io && bulk && M::BULK_RING > 0 && k_push == kb - 1 && kb >= 3) {
             using KB = StepKernelBulk<M, (M::BULK_RING > 0 ? M::BULK_RING : 1)>;

@@ -1185,19 +1185,19 @@ void SparseLU::factor(const double* vals_dev) {
                 }
                 {
                     LuScope ps{"lu_wide_row"};
-                    rt::for_each_block<W_GEMM_THREADS>(
+                    rt::for_each_block<W_GEMM_THREADS, WideCfg::MINB>(
                             (size_t)L.wide_n * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
                             WidePanelKernel<true>{I.fd.ptr(), list, kb, tiles});
                 }
                 {
                     LuScope ps{"lu_wide_gemm"};
-                    rt::for_each_block<W_GEMM_THREADS>(
+                    rt::for_each_block<W_GEMM_THREADS, WideCfg::MINB>(
                             (size_t)L.wide_n * tiles * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
                             WideGemmKernel{I.fd.ptr(), list, kb, tiles});
                 }
                 {
                     LuScope ps{"lu_wide_col"};
-                    rt::for_each_block<W_GEMM_THREADS>(
+                    rt::for_each_block<W_GEMM_THREADS, WideCfg::MINB>(
                             (size_t)L.wide_n * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
                             WidePanelKernel<false>{I.fd.ptr(), list, kb, tiles});
                 }

@@ -29,12 +29,36 @@
 
 constexpr int WB = 128;  //!< pivots per superblock
 constexpr int WT = 128;  //!< tile edge of the panel / trailing GEMMs
-constexpr int WK = 32;   //!< K chunk staged per pipeline stage
-constexpr int WLDA = WT + 4;  //!< A stage: [WK][WLDA], conflict-free fragment loads
-constexpr int WLDB = WK + 4;  //!< B stage: [WT][WLDB]
-constexpr int W_STAGE_DOUBLES = WK * WLDA + WT * WLDB;
-constexpr size_t W_GEMM_SMEM = 2 * (size_t)W_STAGE_DOUBLES * sizeof(double);
-constexpr int W_GEMM_THREADS = 256;
+
+/*! Shape of the tile kernel: WM x WN warps, each MT x NT DMMA tiles of 8 x 8
+ * (WM MT 8 = WN NT 8 = WT), K staged WK deep in STAGES buffers.
+ * Shared-memory strides WT + 4 / WK + 4 (= 4 mod 16 doubles) make the fragment
+ * loads of a half-warp hit 16 distinct 8-byte banks. */
+template <int WM_, int WN_, int WK_, int STAGES_, int MINB_>
+struct WideCfgT {
+    static constexpr int WM = WM_, WN = WN_, WK = WK_, STAGES = STAGES_, MINB = MINB_;
+    static constexpr int MT = WT / 8 / WM, NT = WT / 8 / WN;
+    static constexpr int THREADS = 32 * WM * WN;
+    static constexpr int LDA = WT + 4, LDB = WK + 4;
+    static constexpr int STAGE_DOUBLES = WK * LDA + WT * LDB;
+    static constexpr size_t SMEM = (size_t)STAGES * STAGE_DOUBLES * sizeof(double);
+    static_assert(WM * MT * 8 == WT && WN * NT * 8 == WT && WK % 4 == 0 &&
+                          (LDB % 16) == 4,
+                  "tile shape");
+};
+//! 8 warps of 64 x 32, one CTA per SM (206 registers)
+using WideCfgBig = WideCfgT<2, 4, 32, 2, 1>;
+//! 16 warps of 32 x 32 (a 128 x 128 FP64 accumulator tile is half of the SM's
+//! register file, so one CTA per SM either way), K staged 16 deep in 3 buffers
+using WideCfgDual = WideCfgT<4, 4, 16, 3, 1>;
+#ifndef SANM_WIDE_CFG
+#define SANM_WIDE_CFG WideCfgDual
+#endif
+using WideCfg = SANM_WIDE_CFG;
+constexpr size_t W_GEMM_SMEM =
+        WideCfg::SMEM > (size_t)WT * WT * sizeof(double) ? WideCfg::SMEM
+                                                         : (size_t)WT * WT * sizeof(double);
+constexpr int W_GEMM_THREADS = WideCfg::THREADS;
 
 enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
 
@@ -81,78 +105,85 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
         }
     }
 #else
+    using G = WideCfg;
+    constexpr int WK = G::WK, MT = G::MT, NT = G::NT, LDA = G::LDA, LDB = G::LDB;
     double* sm = reinterpret_cast<double*>(c.smem);
     const int tid = c.tid, lane = tid & 31, warp = tid >> 5;
-    const int wm = warp & 1, wn = warp >> 1;  // 2 x 4 warps, 64 x 32 each
+    const int wm = warp % G::WM, wn = warp / G::WM;
     const int g = lane >> 2, t4 = lane & 3;
-    double acc[8][4][2];
+    double acc[MT][NT][2];
 
-    auto stage_ptr = [&](int s) { return sm + (size_t)s * W_STAGE_DOUBLES; };
+    auto stage_ptr = [&](int s) { return sm + (size_t)s * G::STAGE_DOUBLES; };
     auto load_stage = [&](int s, uint32_t k0) {
         double* As = stage_ptr(s);
-        double* Bs = As + WK * WLDA;
+        double* Bs = As + WK * LDA;
         const uint32_t kk = k - k0 < (uint32_t)WK ? k - k0 : (uint32_t)WK;
         // A chunk: WK columns (q) of WT rows; consecutive threads -> rows
-        for (int e = tid; e < WK * WT; e += W_GEMM_THREADS) {
+        for (int e = tid; e < WK * WT; e += G::THREADS) {
             const uint32_t q = e / WT, i = e % WT;
             const bool ok = q < kk && i < m;
             const double* src = ok ? Ap + (uint64_t)(k0 + q) * lda + i : Ap;
-            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(As + q * WLDA + i);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(As + q * LDA + i);
             asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst),
                          "l"(src), "r"(ok ? 8 : 0)
                          : "memory");
         }
         // B chunk: WT columns (j) of WK rows (q); consecutive threads -> q
-        for (int e = tid; e < WT * WK; e += W_GEMM_THREADS) {
+        for (int e = tid; e < WT * WK; e += G::THREADS) {
             const uint32_t j = e / WK, q = e % WK;
             const bool ok = q < kk && j < n;
             const uint32_t qq = ok ? (kperm ? kperm[k0 + q] : k0 + q) : 0;
             const double* src = ok ? Bp + (uint64_t)j * ldb + qq : Bp;
-            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(Bs + j * WLDB + q);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(Bs + j * LDB + q);
             asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst),
                          "l"(src), "r"(ok ? 8 : 0)
                          : "memory");
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    auto commit = [] { asm volatile("cp.async.commit_group;" ::: "memory"); };
 
     const uint32_t nchunk = (k + WK - 1) / WK;
-    load_stage(0, 0);
+    // prologue: STAGES - 1 chunks in flight (empty groups keep the count)
+#pragma unroll
+    for (int s = 0; s < G::STAGES - 1; ++s) {
+        if ((uint32_t)s < nchunk) load_stage(s, s * WK);
+        commit();
+    }
     // W_SUB: the accumulators start from the C tile and the MMAs run with -A,
     // so that the tile is read once, up front, with all of its loads in flight
-    // behind the first operand stage, and the epilogue only stores (a
+    // behind the first operand stages, and the epilogue only stores (a
     // read-modify-write epilogue of 64 dependent round trips per thread cost
     // twice the time of the MMAs: ncu long-scoreboard 57 % of the samples).
 #pragma unroll
-    for (int mt = 0; mt < 8; ++mt) {
-        const uint32_t row = wm * 64 + mt * 8 + g;
+    for (int mt = 0; mt < MT; ++mt) {
+        const uint32_t row = wm * (MT * 8) + mt * 8 + g;
         const bool rok = MODE == W_SUB && row < m && !(row >= rs0 && row < rs1);
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
+        for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const uint32_t col = wn * 32 + nt * 8 + 2 * t4 + h;
+                const uint32_t col = wn * (NT * 8) + nt * 8 + 2 * t4 + h;
                 const bool ok = rok && col < n && !(col >= cs0 && col < cs1);
                 acc[mt][nt][h] = ok ? Cp[(uint64_t)col * ldc + row] : 0.0;
             }
         }
     }
     for (uint32_t kc = 0; kc < nchunk; ++kc) {
-        if (kc + 1 < nchunk) {
-            load_stage((kc + 1) & 1, (kc + 1) * WK);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        if (kc + G::STAGES - 1 < nchunk) {
+            load_stage((kc + G::STAGES - 1) % G::STAGES, (kc + G::STAGES - 1) * WK);
         }
+        commit();
+        // all but the newest STAGES - 1 groups are complete: chunk kc is in
+        asm volatile("cp.async.wait_group %0;" ::"n"(G::STAGES - 1) : "memory");
         __syncthreads();
-        const double* As = stage_ptr(kc & 1);
-        const double* Bs = As + WK * WLDA;
+        const double* As = stage_ptr(kc % G::STAGES);
+        const double* Bs = As + WK * LDA;
 #pragma unroll
         for (int ks = 0; ks < WK / 4; ++ks) {
-            double a[8], b[4];
+            double a[MT], b[NT];
 #pragma unroll
-            for (int mt = 0; mt < 8; ++mt) {
-                a[mt] = As[(ks * 4 + t4) * WLDA + wm * 64 + mt * 8 + g];
+            for (int mt = 0; mt < MT; ++mt) {
+                a[mt] = As[(ks * 4 + t4) * LDA + wm * (MT * 8) + mt * 8 + g];
                 if (MODE != W_SET) {
                     // -A: flip the sign bit (integer pipe)
                     a[mt] = __longlong_as_double(__double_as_longlong(a[mt]) ^
@@ -160,13 +191,13 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
                 }
             }
 #pragma unroll
-            for (int nt = 0; nt < 4; ++nt) {
-                b[nt] = Bs[(wn * 32 + nt * 8 + g) * WLDB + ks * 4 + t4];
+            for (int nt = 0; nt < NT; ++nt) {
+                b[nt] = Bs[(wn * (NT * 8) + nt * 8 + g) * LDB + ks * 4 + t4];
             }
 #pragma unroll
-            for (int mt = 0; mt < 8; ++mt) {
+            for (int mt = 0; mt < MT; ++mt) {
 #pragma unroll
-                for (int nt = 0; nt < 4; ++nt) {
+                for (int nt = 0; nt < NT; ++nt) {
                     asm volatile(
                             "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 "
                             "{%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -179,14 +210,14 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
     }
     // epilogue: thread holds C(row, col) and C(row, col + 1)
 #pragma unroll
-    for (int mt = 0; mt < 8; ++mt) {
-        const uint32_t row = wm * 64 + mt * 8 + g;
+    for (int mt = 0; mt < MT; ++mt) {
+        const uint32_t row = wm * (MT * 8) + mt * 8 + g;
         if (row >= m || (row >= rs0 && row < rs1)) continue;
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) {
+        for (int nt = 0; nt < NT; ++nt) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const uint32_t col = wn * 32 + nt * 8 + 2 * t4 + h;
+                const uint32_t col = wn * (NT * 8) + nt * 8 + 2 * t4 + h;
                 if (col >= n || (col >= cs0 && col < cs1)) continue;
                 // W_SUB: C - A B ; W_SETNEG: -(A B) ; W_SET: A B
                 Cp[(uint64_t)col * ldc + row] = acc[mt][nt][h];
