@@ -232,162 +232,6 @@ struct StepKernel {
     }
 };
 
-#ifndef SANM_HOSTEMU
-/* ---- order step with the Taylor slots staged by the copy engine ------------
- * Same arithmetic as StepKernel<M, true> for the steady-state step of a sweep
- * (k_push = kb - 1 >= 2).  A (tile, order) slot is one contiguous S KB block of
- * the arena, so the convolution operands are fetched with bulk asynchronous
- * copies (cp.async.bulk, completion on an mbarrier) into a ring of RING slots in
- * shared memory, issued by one thread in consumption order and refilled as
- * soon as a pair has been moved to registers.  Memory-level parallelism then
- * costs shared memory instead of registers and resident blocks: StepKernel
- * needs 5 blocks of 96 registers (with spills) per SM to keep enough loads in
- * flight and stalls at 0.85-0.89 of the copy bandwidth (ncu: 30 % warps
- * active, long-scoreboard 24 cycles per issue); here 2 blocks per SM hold up to
- * 8 slots (150 KB) in flight and the compiler has 255 registers.  The slot
- * of order kb - 1, which this launch has just finished, is taken from
- * registers instead of being read back. */
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    uint32_t done = 0;
-    while (!done) {
-        asm volatile(
-                "{\n\t.reg .pred p;\n\t"
-                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                "selp.u32 %0, 1, 0, p;\n\t}"
-                : "=r"(done)
-                : "r"(addr), "r"(parity)
-                : "memory");
-    }
-}
-
-template <class M, int RING>
-struct StepKernelBulk {
-    KArgs a;
-    IOArgs io;
-    int k_push, kb;
-    static constexpr int S = M::S;
-    static constexpr uint32_t SLOT_DOUBLES = S * TILE;
-    static constexpr uint32_t SLOT_BYTES = SLOT_DOUBLES * sizeof(double);
-    static constexpr size_t SMEM =
-            (12 * TILE + (size_t)RING * SLOT_DOUBLES) * sizeof(double) +
-            RING * sizeof(uint64_t);
-
-    //! order of the q-th slot fetched: 1, then (i, kb - i) for i = 2 .. with
-    //! 2 i < kb, then kb / 2 when kb is even
-    __device__ int seq(int q) const {
-        if (q == 0) return 1;
-        const int i = (q - 1) / 2 + 2;
-        if (2 * i < kb) return ((q - 1) & 1) ? kb - i : i;
-        return kb / 2;
-    }
-
-    __device__ void operator()(const rt::BlockCtx& c) const {
-        double* vals = reinterpret_cast<double*>(c.smem);
-        double* ring = vals + 12 * TILE;
-        uint64_t* bar = reinterpret_cast<uint64_t*>(ring + (size_t)RING * SLOT_DOUBLES);
-        const int lane = c.tid;
-        const size_t t = c.bid * TILE + lane;
-        const bool valid = t < a.n;
-        const double* tile_base = a.arena + (size_t)c.bid * a.K1 * SLOT_DOUBLES;
-        const int imax = (kb - 1) / 2;  // pairs (i, kb - i), i = 1 .. imax
-        const int nload = 1 + 2 * (imax - 1) + (kb % 2 == 0 ? 1 : 0);
-
-        auto issue = [&](int q) {
-            const int b = q % RING;
-            const uint32_t bar_a = smem_u32(bar + b);
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_a),
-                         "r"(SLOT_BYTES)
-                         : "memory");
-            asm volatile(
-                    "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes "
-                    "[%0], [%1], %2, [%3];" ::"r"(smem_u32(ring + (size_t)b * SLOT_DOUBLES)),
-                    "l"(tile_base + (size_t)seq(q) * SLOT_DOUBLES), "r"(SLOT_BYTES),
-                    "r"(bar_a)
-                    : "memory");
-        };
-        if (c.tid == 0) {
-            for (int b = 0; b < RING; ++b) {
-                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar + b)));
-            }
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            for (int q = 0; q < RING && q < nload; ++q) issue(q);
-        }
-        __syncthreads();  // barriers initialised before anybody waits on them
-
-        // ---- coefficient phase of order k_push (as StepKernel)
-        double s0[S], aux[M::AUX ? M::AUX : 1], sk[S];
-        if (valid) {
-            ld_strided<S>(s0, slot_ptr<M>(a, t, 0));
-            if (M::AUX) ld_strided<M::AUX>(aux, aux_ptr<M>(a, t));
-            double Ds[9], dm[9], Pt[9];
-            load_ds<true>(Ds, a, io, t);
-            ld_soa<9>(dm, a.dminv, a.npad, t);
-            taylor::mm3(sk, Ds, dm);  // F_k
-            M::tangent(sk, s0, aux, a.pr, sk, Pt);
-            double* pk = slot_ptr<M>(a, t, k_push);
-#pragma unroll
-            for (int q = 9; q < S; ++q) sk[q] += pk[q * TILE];  // bias parts (k_push >= 2)
-            st_strided<S>(pk, sk);
-        }
-
-        // ---- convolutions of order kb from the ring
-        typename M::Acc acc;
-        M::zero(acc);
-        int q = 0;  // next slot to consume
-        auto take = [&](double* dst) {
-            const int b = q % RING;
-            mbar_wait(bar + b, (uint32_t)(q / RING) & 1u);
-            const double* src = ring + (size_t)b * SLOT_DOUBLES + lane;
-#pragma unroll
-            for (int e = 0; e < S; ++e) dst[e] = src[e * TILE];
-            ++q;
-        };
-        double Si[S], Sj[S];
-        {
-            take(Si);  // slot 1 against slot kb - 1 = sk
-            __syncthreads();
-            if (c.tid == 0 && q - 1 + RING < nload) issue(q - 1 + RING);
-            if (valid) {
-                M::accum(acc, Si, sk, 1, kb - 1);
-                M::accum(acc, sk, Si, kb - 1, 1);
-            }
-        }
-        for (int i = 2; i <= imax; ++i) {
-            const int j = kb - i;
-            take(Si);
-            take(Sj);
-            __syncthreads();
-            if (c.tid == 0) {
-                if (q - 2 + RING < nload) issue(q - 2 + RING);
-                if (q - 1 + RING < nload) issue(q - 1 + RING);
-            }
-            if (valid) {
-                M::accum(acc, Si, Sj, i, j);
-                M::accum(acc, Sj, Si, j, i);
-            }
-        }
-        if (kb % 2 == 0) {
-            take(Si);
-            if (valid) M::accum(acc, Si, Si, kb / 2, kb / 2);
-        }
-        if (valid) {
-            double bs[S], Pb[9];
-            M::bias(acc, s0, aux, kb, a.pr, bs, Pb);
-            double* pb = slot_ptr<M>(a, t, kb);
-#pragma unroll
-            for (int e = 9; e < S; ++e) pb[e * TILE] = bs[e];
-            emit_forces(vals, lane, Pb, a, io, t);
-        }
-        __syncthreads();
-        block_reduce(c, vals, io);
-    }
-};
-#endif  // !SANM_HOSTEMU
-
 //! forward-mode Jacobian: nine unit tangents per tet, stored
 //! structure-of-arrays [81][npad] (entry o * 9 + j) so that stores coalesce
 template <class M>
@@ -505,23 +349,6 @@ void FusedProp::launch_step(int k_push, int kb, bool want_out, const double* x) 
         // the kernel is HBM-bound and wants as many loads in flight as the
         // register file allows; __launch_bounds__(128, 1) (255 registers) gives
         // 1.76 G tet*order/s where (128, 5) gives 2.49 G
-#ifndef SANM_HOSTEMU
-        // SANM_STEP_BULK=1: slots staged by bulk copies (StepKernelBulk above).
-        // Opt-in: measured SLOWER than the register-staged kernel on the B200
-        // (2 M tets, K = 20: NH-C 1.95 vs 2.50 G tet*order/s, ARAP 1.47 vs 1.57)
-        // -- two blocks per SM leave the SM idle during each block's gather /
-        // assembly phases and keep only ~2 slots per block in flight.
-        static const bool bulk = [] {
-            const char* e = getenv("SANM_STEP_BULK");
-            return e && e[0] == '1';
-        }();
-        if (use_io && bulk && M::BULK_RING > 0 && k_push == kb - 1 && kb >= 3) {
-            using KB = StepKernelBulk<M, (M::BULK_RING > 0 ? M::BULK_RING : 1)>;
-            rt::for_each_block<TILE, M::BULK_BLOCKS>(ntiles, TILE, KB::SMEM,
-                                                     KB{a, io, k_push, kb});
-            return;
-        }
-#endif
         if (use_io) {
             rt::for_each_block<TILE, M::MINB>(
                     ntiles, TILE, smem,

@@ -130,10 +130,6 @@ struct NHC {
     //! unbounded (ptxas picks 128 regs = 4 blocks) 2.43 G tet*order/s, 4: 2.43,
     //! 5: 2.49, 6: 2.33 (spills)
     static constexpr int MINB = 5;
-    //! bulk-copy order step (fused.cu StepKernelBulk): shared-memory ring of
-    //! this many S KB slots, resident blocks per SM it is compiled for
-    static constexpr int BULK_RING = 4;
-    static constexpr int BULK_BLOCKS = 2;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18 };
     struct Acc {
@@ -216,10 +212,6 @@ struct NHI {
     static constexpr int S = 23;
     //! unbounded (236 regs = 2 blocks) 1.61 G, 4: 1.85, 5: 1.61
     static constexpr int MINB = 4;
-    //! bulk-copy order step (fused.cu StepKernelBulk): shared-memory ring of
-    //! this many S KB slots, resident blocks per SM it is compiled for
-    static constexpr int BULK_RING = 4;
-    static constexpr int BULK_BLOCKS = 2;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18, oJ = 19, oQ = 20, oI = 21, oT = 22 };
     struct Acc {
@@ -339,10 +331,6 @@ struct ARAP {
     static constexpr int S = 27;
     //! unbounded (240 regs = 2 blocks) 1.43 G, 4: 1.56, 5: 1.55
     static constexpr int MINB = 4;
-    //! bulk-copy order step (fused.cu StepKernelBulk): shared-memory ring of
-    //! this many S KB slots, resident blocks per SM it is compiled for
-    static constexpr int BULK_RING = 3;
-    static constexpr int BULK_BLOCKS = 2;
     static constexpr int AUX = 12;
     enum { oF = 0, oP = 9, oW = 18 };
     struct Acc {

@@ -46,13 +46,15 @@ struct WideCfgT {
                           (LDB % 16) == 4,
                   "tile shape");
 };
-//! 8 warps of 64 x 32, one CTA per SM (206 registers)
+//! 8 warps of 64 x 32, one CTA per SM (227 registers): 21.4 TFLOP/s on the
+//! trailing updates of the 1 M-tet cuboid (default)
 using WideCfgBig = WideCfgT<2, 4, 32, 2, 1>;
 //! 16 warps of 32 x 32 (a 128 x 128 FP64 accumulator tile is half of the SM's
-//! register file, so one CTA per SM either way), K staged 16 deep in 3 buffers
+//! register file, so one CTA per SM either way), K staged 16 deep in 3 buffers:
+//! measured 8 % slower than WideCfgBig (19.8 TFLOP/s)
 using WideCfgDual = WideCfgT<4, 4, 16, 3, 1>;
 #ifndef SANM_WIDE_CFG
-#define SANM_WIDE_CFG WideCfgDual
+#define SANM_WIDE_CFG WideCfgBig
 #endif
 using WideCfg = SANM_WIDE_CFG;
 constexpr size_t W_GEMM_SMEM =
