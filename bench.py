@@ -606,6 +606,30 @@ def side_energy(b, torch, stream, energy, peak, steps=5, warmup=3,
     return out
 
 
+def bind_to_gpu_numa_node(torch, local_rank):
+    """Run this rank on the cores of the NUMA node its GPU hangs off, BEFORE
+    the pinned host buffers are allocated (first touch puts them there): with
+    8 ranks on one host the copies of the e2e path otherwise cross sockets.
+    Returns a short description for the JSON line."""
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return "numa node unknown"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"numa node {node}: no allowed cores"
+        os.sched_setaffinity(0, cpus)
+        return f"numa node {node}, {len(cpus)} cores"
+    except Exception as e:  # plumbing only: never fail the run over it
+        return f"not bound ({type(e).__name__})"
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -619,6 +643,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device(
             "cuda", local_rank))
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa_node(torch, local_rank) if world > 1 else "single rank"
     b = sanm_b200.load()
     b.call("set_device", ctypes.c_int(local_rank))
     # a dedicated (non-default) stream shared by torch's events and the
@@ -721,6 +746,24 @@ def run_ours(args):
         dist.all_reduce(nbytes, op=dist.ReduceOp.SUM)
     ms_total, ms_e2e = (float(v) for v in t.cpu())
     h2d_bytes, d2h_bytes = (int(v) for v in nbytes.cpu())
+    # N > 1: the same sweep WITHOUT the exchange step = what one GPU does alone
+    # on its 2.0 M tets, measured in this run on this box (the N = 1 line of a
+    # default run is on the 10 M-tet contract config, a different per-GPU size)
+    ms_local = None
+    if world > 1:
+        sweep.set_exchange(2)
+        for _ in range(2):
+            sweep.run()
+        barrier()
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            sweep.run()
+        e1.record(stream)
+        barrier()
+        tl = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tl, op=dist.ReduceOp.MAX)
+        ms_local = float(tl.cpu()[0])
     big_row = None
     if not args.no_solves:
         # all ranks: the drivers exchange right-hand sides and K values
@@ -810,6 +853,15 @@ def run_ours(args):
     ref = None
     if os.path.exists(ORACLE_LIB):
         ref = load_oracle()
+    if ms_local is not None:
+        per_gpu = float(n_tets) * ORDER * args.steps / (ms_local * 1e-3)
+        line["weak_scaling"] = {
+            "per_gpu_value_without_exchange": per_gpu,
+            "efficiency_vs_same_size_single_gpu": value / (world * per_gpu),
+            "note": "same sweep, same 2.0 M tets per GPU, exchange step "
+                    "switched off (slowest rank); the N = 1 line of a default "
+                    "run uses the 10 M-tet contract config instead",
+            "host_placement": numa}
     if big_row is not None:
         line["solve_at_scale"] = big_row
     if world == 1 and not args.no_energies:

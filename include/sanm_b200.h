@@ -196,7 +196,9 @@ int sanm_sweep_wait_host(sanm_sweep_t* s);
  * distributed: only the interface rows shared with neighbouring ranks are
  * exchanged and summed (ncclSend/ncclRecv), rows outside this rank's range are
  * not touched, and sanm_sweep_run_host() moves only the local ranges of x and
- * b.  Collective: call it on every rank.  (The reference gathers its worker
+ * b.  mode 2: as mode 1 without the exchange itself (measurement aid: the
+ * per-GPU reference point of a scaling run; interface rows stay partial sums).
+ * Collective: call it on every rank.  (The reference gathers its worker
  * shards by memcpy inside one process, libsanm/symbolic.cpp:418-439.) */
 int sanm_sweep_set_exchange(sanm_sweep_t* s, int mode);
 /* ranges4 = {x_lo, x_hi, b_lo, b_hi}: nodal index ranges the local tets read

@@ -52,7 +52,12 @@ public:
      * outside the local range [b_lo, b_hi) are left untouched, and
      * run_host() transfers only the local ranges of x and b. */
     void set_exchange(int mode) {
-        sanm_check(mode == 0 || mode == 1, "exchange mode %d", mode);
+        sanm_check(mode >= 0 && mode <= 2, "exchange mode %d", mode);
+        // 2: like 1 but WITHOUT the exchange step: every rank only assembles
+        // its own tets (per-GPU reference point of a scaling run; the
+        // interface rows are then partial sums)
+        m_no_exchange = mode == 2;
+        if (mode == 2) mode = 1;
         m_halo_mode = mode == 1;
         // distributed nodal vectors: the second assembly level and the zero
         // fills run over this rank's rows only (rows outside [b_lo, b_hi) are
@@ -168,6 +173,7 @@ private:
      * beside the element kernels of the next orders; consumers of b_k (the
      * device->host pipe, the end of the sweep) wait for the side stream. */
     void exchange(double* b) {
+        if (m_no_exchange) return;
         if (m_halo_mode) {
             if (comm::world() > 1 && m_async_halo) {
                 rt::pipe_wait(rt::PIPE_COMM, rt::fence_main());
@@ -288,7 +294,7 @@ private:
     int m_order;
     uint64_t m_nin = 0, m_nout = 0;
     uint64_t m_x_lo = 0, m_x_hi = 0, m_b_lo = 0, m_b_hi = 0;
-    bool m_halo_inflight = false;
+    bool m_halo_inflight = false, m_no_exchange = false;
     //! SANM_SYNC_HALO=1: exchange on the main stream (measurement aid)
     const bool m_async_halo = getenv("SANM_SYNC_HALO") == nullptr;
     bool m_halo_mode = false;
