@@ -71,6 +71,9 @@ def parse_args():
                     help="skip the fea end-to-end solve section")
     ap.add_argument("--no-cpu", action="store_true",
                     help="skip the cpu_baseline leg")
+    ap.add_argument("--sweep-x", action="store_true",
+                    help="N = 1: also measure the SURVEY 8d size sweep "
+                         "x in {51,101,201,401} (y, z as the workload)")
     ap.add_argument("--no-energies", action="store_true",
                     help="skip the NH-I / ARAP side measurements")
     ap.add_argument("--cpu-tets", type=int, default=1000000,
@@ -864,6 +867,12 @@ def run_ours(args):
             "host_placement": numa}
     if big_row is not None:
         line["solve_at_scale"] = big_row
+    if world == 1 and args.sweep_x:
+        # element/assembly scaling sweep over the cuboid length
+        line["size_sweep"] = [
+            side_energy(b, torch, stream, args.energy, peak,
+                        dims=(nx, args.ny, args.nz))
+            for nx in (51, 101, 201, 401) if nx != args.nx]
     if world == 1 and not args.no_energies:
         line["energies"] = [side_energy(b, torch, stream, e, peak)
                             for e in ("neohookean_i", "arap")
