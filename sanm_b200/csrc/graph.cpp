@@ -322,10 +322,10 @@ Lowered lower_graph(const Graph& g, int out_var, const Shape& x_shape) {
                 sanm_check(s.rank == 3 && s.dim[1] == s.dim[2],
                            "invalid shape for det: %s", s.str().c_str());
                 sanm_check(s.dim[1] > 1, "scalar determinant is unsupported");
-                sanm_check(s.dim[1] <= 3,
-                           "determinant of %zux%zu matrices is not implemented "
-                           "on the device path (2x2 and 3x3 only)",
-                           (size_t)s.dim[1], (size_t)s.dim[1]);
+                sanm_check(s.dim[1] <= (uint64_t)MAXD,
+                           "determinant of %zux%zu matrices: dims above %d are "
+                           "not supported on the device path",
+                           (size_t)s.dim[1], (size_t)s.dim[1], MAXD);
                 o0.shape = Shape{s.dim[0], 1};
                 break;
             }
@@ -475,6 +475,8 @@ Lowered lower_graph(const Graph& g, int out_var, const Shape& x_shape) {
                     L.vars[lo.in[0]].needs_stack = true;
                     lo.esb = 1;
                     if (L.vars[lo.in[0]].d1 == 3) lo.eauxk = 3;
+                    // m >= 4: [G_j, T_j, D_j] per order (taylor_dev.h op_det)
+                    if (L.vars[lo.in[0]].d1 >= 4) lo.eauxk = L.vars[lo.in[0]].e + 2;
                 }
                 break;
             case OP_MATINVMUL:

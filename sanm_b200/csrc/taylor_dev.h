@@ -974,10 +974,16 @@ SANM_HD inline void cross3(double* r, const double* a, const double* b) {
  * (3 doubles per order) makes the self-bias an O(k) sum:
  *   self_bias_k = sum_{i=1}^{k-1} r0_i . c_{k-i}  +  r0_0 . cp_k,
  *   cp_k = sum_{i=1}^{k-1} r1_i x r2_{k-i},   c_k = cp_k + r1_0 x r2_k + r1_k x r2_0.
- * 2x2: direct convolution.  Other sizes: direct truncated polynomial expansion
- * over row permutations is not implemented on the device; sizes 4..MAXD use
- * evaluate-at-points interpolation-free O(k^2) Leibniz recursion on minors is
- * left for a later round (the lowering rejects them).
+ * 2x2: direct convolution.  m >= 4 (the reference expands the polynomial
+ * determinant, libsanm/tensor_polymat.cpp:30-136,138-341, O(k^2) per order):
+ * here the series of det X follows from (det X)' = det X tr(X^-1 X'):
+ *     G = X^-1 :   G_k = -G_0 sum_{i=1}^{k} X_i G_{k-i}
+ *     T = tr(G X'): T_n = sum_{p+q=n} (q+1) tr(G_p X_{q+1})
+ *     k D_k = sum_{i=0}^{k-1} D_i T_{k-1-i}
+ * The only term of D_k with the unknown X_k is D_0 k tr(G_0 X_k) / k =
+ * <cof X_0, X_k>, so the self-bias is everything else.  Hidden stack per
+ * order j: [G_j (m^2), T_j, D_j]; O(k m^3) per order.  Needs det X_0 != 0
+ * (as every use of the determinant in `fea` and in the reference's tests).
  */
 SANM_HD inline void op_det(const DOp& op, const ItemCtx& c) {
     const int x = op.in[0], o = op.out[0];
@@ -995,6 +1001,11 @@ SANM_HD inline void op_det(const DOp& op, const ItemCtx& c) {
             double cr[3];
             cross3(cr, X + 3, X + 6);
             st_buf<3>(op.auxk, cr, np, t, 3);  // slot 0
+        } else if (m >= 4 && op.auxk) {
+            double G[MAXE];
+            inv_n(G, X, m);
+            st_buf<0>(op.auxk, G, np, t, xv.e);
+            op.auxk[(int64_t)(xv.e + 1) * np + t] = det_n(X, m);  // D_0
         }
         return;
     }
@@ -1055,12 +1066,61 @@ SANM_HD inline void op_det(const DOp& op, const ItemCtx& c) {
         } else if (!c.sb_zero) {
             sb = op.sb[t];
         }
+    } else {
+        // m >= 4: hidden slot j = [G_j (E), T_j, D_j]
+        const int E = xv.e;
+        auto slot = [&](int j) { return op.auxk + (int64_t)j * op.auxk_stride + t; };
+        auto tr_gx = [&](int p, int q) {  // tr(G_p X_q)
+            const double* g = slot(p);
+            const double* xq = vbase(xv, q) + t;
+            double s = 0;
+            for (int r = 0; r < m; ++r) {
+                for (int cc = 0; cc < m; ++cc) {
+                    s += g[(int64_t)(r * m + cc) * np] * xq[(int64_t)(cc * m + r) * np];
+                }
+            }
+            return s;
+        };
+        if (c.phase == PH_BIAS) {
+            double s1 = 0, s2 = 0;
+            for (int i = 1; i < k; ++i) {
+                s1 += slot(i)[(int64_t)(E + 1) * np] * slot(k - 1 - i)[(int64_t)E * np];
+            }
+            for (int p = 1; p < k; ++p) s2 += (double)(k - p) * tr_gx(p, k - p);
+            const double d0 = slot(0)[(int64_t)(E + 1) * np];
+            sb = (s1 + d0 * s2) / (double)k;
+            op.sb[t] = sb;
+            slot(k - 1)[(int64_t)E * np] = s2;  // known part of T_{k-1}
+        } else {
+            double tpart = 0;
+            if (!c.sb_zero) {
+                sb = op.sb[t];
+                tpart = slot(k - 1)[(int64_t)E * np];
+            }
+            // T_{k-1} complete, G_k = -G_0 sum_{i=1}^{k} X_i G_{k-i}
+            slot(k - 1)[(int64_t)E * np] = tpart + (double)k * tr_gx(0, k);
+            double acc[MAXE], A[MAXE], B[MAXE];
+            for (int e = 0; e < E; ++e) acc[e] = 0;
+            for (int i = 1; i <= k; ++i) {
+                ld_mat<0>(A, xv, i, np, t, E);
+                ld_buf<0>(B, op.auxk + (int64_t)(k - i) * op.auxk_stride, np, t, E);
+                mm_acc<0, 0, 0>(acc, A, B, m, m, m);
+            }
+            ld_buf<0>(A, op.auxk, np, t, E);  // G_0
+            for (int e = 0; e < E; ++e) B[e] = 0;
+            mm_acc<0, 0, 0>(B, A, acc, m, m, m);
+            for (int e = 0; e < E; ++e) B[e] = -B[e];
+            st_buf<0>(op.auxk + (int64_t)k * op.auxk_stride, B, np, t, E);
+        }
     }
     double r = sb;
     for (int e = 0; e < xv.e; ++e) {
         r += op.aux0[(int64_t)e * np + t] * c.ld(x, k, e);
     }
     c.st(o, k, 0, r);
+    if (m >= 4 && c.phase != PH_BIAS) {
+        op.auxk[(int64_t)k * op.auxk_stride + (int64_t)(xv.e + 1) * np + t] = r;  // D_k
+    }
 }
 
 /*!

@@ -154,3 +154,22 @@ def test_matinvmul_nonsquare_matmul(impl, ref):
         return z.batched_matmul(g.constant(c)).batched_transpose()
 
     compare(impl, ref, build, xs, order)
+
+
+@pytest.mark.parametrize("m", [2, 4, 5, 7])
+def test_batched_det_other_sizes(impl, ref, m):
+    """Symbolic.BatchDeterminant for the sizes of tests/symbolic.cpp:324-358
+    (`batched_det-mid` 4, `-large0` 5, `-large1` 7; y = det(x) * x): the
+    reference expands the polynomial determinant (tensor_polymat.cpp:30-341),
+    the device path integrates (det X)' = det X tr(X^-1 X') (taylor_dev.h
+    op_det); both against each other at every order"""
+    rng = np.random.default_rng(40 + m)
+    n, order = 10, 10
+    xs = [rng.uniform(-1, 1, (n, m, m)) + 2.5 * np.eye(m)[None]]
+    xs += [rng.uniform(-1, 1, (n, m, m)) * 0.5 ** k for k in range(1, order + 1)]
+
+    def build(g):
+        x = g.placeholder()
+        return x.batched_det() * x
+
+    compare(impl, ref, build, xs, order)
