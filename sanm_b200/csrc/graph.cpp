@@ -506,18 +506,20 @@ Lowered lower_graph(const Graph& g, int out_var, const Shape& x_shape) {
     L.elemwise = elemwise &&
                  L.vars[L.input].e == L.vars[L.output].e;
 
-    // polar mode only: U and S of an SVD-W that depends on the input must not
-    // be read by anything (libsanm/oprs/linalg.cpp:529-543)
+    // SVD-W mode (libsanm/oprs/linalg.cpp:529-543): polar when neither U nor S
+    // of an SVD-W that depends on the input is read, full otherwise
     std::vector<int> readers(L.vars.size(), 0);
     for (auto& lo : L.ops) {
         for (int v : lo.in) ++readers[v];
     }
     ++readers[L.output];
     for (auto& lo : L.ops) {
-        if (lo.type == OP_SVDW && !lo.const_op) {
-            sanm_check(!readers[lo.out[0]] && !readers[lo.out[1]],
-                       "only the polar mode of SVD-W (outputs U and S unread) "
-                       "is implemented on the device path");
+        if (lo.type == OP_SVDW && !lo.const_op &&
+            (readers[lo.out[0]] || readers[lo.out[1]])) {
+            lo.svdw_full = true;
+            for (int q = 0; q < 3; ++q) L.vars[lo.out[q]].needs_stack = true;
+            lo.esb = 27;    // Bu, Bw, Mbias
+            lo.eauxk = 18;  // (U S)_k, (U S U^T)_k
         }
     }
     return L;

@@ -111,6 +111,7 @@ struct LoweredOp {
     int eaux0 = 0;  //!< doubles of order-0 cache per item
     int eauxk = 0;  //!< doubles of hidden per-order stack per item
     bool need_flag = false;
+    bool svdw_full = false;  //!< SVD-W: U or S has readers (full mode)
 };
 
 struct Lowered {

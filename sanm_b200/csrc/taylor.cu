@@ -219,6 +219,7 @@ void TaylorProp::prepare(const Shape& x_shape) {
                 break;
             case OP_SVDW:
                 d.i[0] = go.ip[0];
+                d.i[1] = o.svdw_full;
                 break;
             case OP_SLICE: {
                 // resolve begin against the per-item axis size

@@ -597,6 +597,72 @@ SANM_HD inline void svdw3_fwd_p(double* Pk, double* Wk, const double* Mk,
         for (int c = 0; c < 3; ++c) Wk[r * 3 + c] = WkT[c * 3 + r];
 }
 
+/*!
+ * Order-k FULL-mode forward solve (U_k, S_k, W_k all wanted), restating
+ * svd_w_taylor_fwd (libsanm/tensor_svd.cpp:275-387) on row-major 3x3 arrays.
+ * M = U S U^T W;  Mb = the part of [U S U^T W]_k without order-k unknowns,
+ * Bu = sum U_i^T U_{k-i},  Bw = sum W_i^T W_{k-i}  (i = 1 .. k-1).  With
+ * V0 = W0^T U0:
+ *   E  = V0^T (Mk - Mb)^T U0
+ *   R  = E^T - E - V0^T Bw V0 diag(S0);   X_ij = clip_div(R_ij, S0_i + S0_j)
+ *   Wk = U0 X V0^T
+ *   E' = E - X^T diag(S0) + Bu^T diag(S0);   Sk_i = E'_ii
+ *   Q_ij = clip_div(E'_ij, S0_i - S0_j), Q_ji = -Bu_ij - Q_ij (i < j),
+ *   Q_jj = -Bu_jj / 2;   Uk = U0 Q^T
+ */
+SANM_HD inline void svdw3_fwd_full(double* Uk, double* Sk, double* Wk,
+                                   const double* Mk, const double* Mb,
+                                   const double* U0, const double* S0,
+                                   const double* W0, const double* Bu,
+                                   const double* Bw) {
+    double V0[9], D[9], t0[9], t1[9], E[9], X[9];
+    mm3_tn(V0, W0, U0);  // W0^T U0
+#pragma unroll
+    for (int q = 0; q < 9; ++q) D[q] = Mk[q] - Mb[q];
+    // E = V0^T D^T U0, with V0^T D^T = (D V0)^T
+    mm3(t1, D, V0);
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) t0[r * 3 + c] = t1[c * 3 + r];
+    mm3(E, t0, U0);
+    // R = E^T - E - V0^T Bw V0 diag(S0)
+    mm3_tn(t0, V0, Bw);
+    mm3(t1, t0, V0);
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const double rv = E[c * 3 + r] - E[r * 3 + c] - t1[r * 3 + c] * S0[c];
+            X[r * 3 + c] = clip_div(rv, S0[r] + S0[c]);
+        }
+    // Wk = U0 X V0^T
+    mm3(t0, U0, X);
+    mm3_nt(Wk, t0, V0);
+    // E' = E - X^T diag(S0) + Bu^T diag(S0)
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            E[r * 3 + c] += (Bu[c * 3 + r] - X[c * 3 + r]) * S0[c];
+        }
+    double Q[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        Sk[j] = E[j * 3 + j];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            if (i < j) {
+                const double v = clip_div(E[i * 3 + j], S0[i] - S0[j]);
+                Q[i * 3 + j] = v;
+                Q[j * 3 + i] = -Bu[i * 3 + j] - v;
+            }
+        }
+        Q[j * 3 + j] = -Bu[j * 3 + j] / 2;
+    }
+    mm3_nt(Uk, U0, Q);  // U0 Q^T
+}
+
 /* -------------------------------------------------------- op evaluation */
 
 enum Phase : int {
@@ -1123,10 +1189,137 @@ SANM_HD inline void op_det(const DOp& op, const ItemCtx& c) {
     }
 }
 
+//! orders >= 1 of the full mode of SVD-W, see op_svdw
+SANM_HD inline void op_svdw_full(const DOp& op, const ItemCtx& c) {
+    const DVar &xv = c.var(op.in[0]), &uv = c.var(op.out[0]), &sv = c.var(op.out[1]),
+               &wv = c.var(op.out[2]);
+    const int64_t np = c.np;
+    const size_t t = c.t;
+    const int k = c.k;
+    auto p0_slot = [&](int j) { return op.auxk + (int64_t)j * op.auxk_stride; };
+    auto p1_slot = [&](int j) { return op.auxk + (int64_t)j * op.auxk_stride + 9 * np; };
+    double Bu[9], Bw[9], Mb[9], U0[9], S0[3], W0[9], A[9], B[9], Sv[3];
+    ld_buf<9>(U0, op.aux0, np, t, 9);
+    ld_buf<3>(S0, op.aux0 + 9 * np, np, t, 3);
+    ld_mat<9>(W0, wv, 0, np, t, 9);
+    zero_arr<9>(Bu, 9);
+    zero_arr<9>(Bw, 9);
+    zero_arr<9>(Mb, 9);
+    if (c.phase == PH_BIAS) {
+        double t0[9], t1[9];
+        zero_arr<9>(t0, 9);
+        zero_arr<9>(t1, 9);
+        for (int i = 1; i < k; ++i) {
+            // Bu += U_i^T U_{k-i} ; Bw += W_i^T W_{k-i}
+            ld_mat<9>(A, uv, i, np, t, 9);
+            ld_mat<9>(B, uv, k - i, np, t, 9);
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc)
+                    Bu[r * 3 + cc] += A[r] * B[cc] + A[3 + r] * B[3 + cc] + A[6 + r] * B[6 + cc];
+            // t0 += U_i diag(S_{k-i})   (partial (U S)_k)
+            ld_mat<3>(Sv, sv, k - i, np, t, 3);
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc) t0[r * 3 + cc] += A[r * 3 + cc] * Sv[cc];
+            // t1 += P0_i U_{k-i}^T       (partial (U S U^T)_k)
+            ld_buf<9>(A, p0_slot(i), np, t, 9);
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc)
+                    t1[r * 3 + cc] += A[r * 3] * B[cc * 3] + A[r * 3 + 1] * B[cc * 3 + 1] +
+                                      A[r * 3 + 2] * B[cc * 3 + 2];
+            // Mb += P1_i W_{k-i}
+            ld_buf<9>(A, p1_slot(i), np, t, 9);
+            ld_mat<9>(B, wv, k - i, np, t, 9);
+            mm_acc<3, 3, 3>(Mb, A, B, 3, 3, 3);
+            ld_mat<9>(A, wv, i, np, t, 9);
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc)
+                    Bw[r * 3 + cc] += A[r] * B[cc] + A[3 + r] * B[3 + cc] + A[6 + r] * B[6 + cc];
+        }
+        // t1 += t0 U_0^T ;  Mb += t1 W_0
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int cc = 0; cc < 3; ++cc)
+                t1[r * 3 + cc] += t0[r * 3] * U0[cc * 3] + t0[r * 3 + 1] * U0[cc * 3 + 1] +
+                                  t0[r * 3 + 2] * U0[cc * 3 + 2];
+        mm_acc<3, 3, 3>(Mb, t1, W0, 3, 3, 3);
+        st_buf<9>(op.sb, Bu, np, t, 9);
+        st_buf<9>(op.sb + 9 * np, Bw, np, t, 9);
+        st_buf<9>(op.sb + 18 * np, Mb, np, t, 9);
+    } else if (!c.sb_zero) {
+        ld_buf<9>(Bu, op.sb, np, t, 9);
+        ld_buf<9>(Bw, op.sb + 9 * np, np, t, 9);
+        ld_buf<9>(Mb, op.sb + 18 * np, np, t, 9);
+    }
+    double Mk[9], Uk[9], Sk[3], Wk[9];
+    ld_mat<9>(Mk, xv, k, np, t, 9);
+    svdw3_fwd_full(Uk, Sk, Wk, Mk, Mb, U0, S0, W0, Bu, Bw);
+    st_buf<9>(vbase(uv, k), Uk, np, t, 9);
+    st_buf<3>(vbase(sv, k), Sk, np, t, 3);
+    st_buf<9>(vbase(wv, k), Wk, np, t, 9);
+    if (c.phase == PH_COEF) {
+        // P0_k = sum_{j=0}^{k} U_j diag(S_{k-j}),  P1_k = sum_{j=0}^{k} P0_j U_{k-j}^T
+        double P0[9], P1[9];
+        zero_arr<9>(P0, 9);
+        zero_arr<9>(P1, 9);
+        for (int j = 0; j <= k; ++j) {
+            if (j == k) {
+#pragma unroll
+                for (int q = 0; q < 9; ++q) A[q] = Uk[q];
+            } else {
+                ld_mat<9>(A, uv, j, np, t, 9);
+            }
+            if (j == 0) {
+#pragma unroll
+                for (int q = 0; q < 3; ++q) Sv[q] = Sk[q];
+            } else {
+                ld_mat<3>(Sv, sv, k - j, np, t, 3);
+            }
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc) P0[r * 3 + cc] += A[r * 3 + cc] * Sv[cc];
+        }
+        for (int j = 0; j <= k; ++j) {
+            if (j == k) {
+#pragma unroll
+                for (int q = 0; q < 9; ++q) A[q] = P0[q];
+            } else {
+                ld_buf<9>(A, p0_slot(j), np, t, 9);
+            }
+            if (j == 0) {
+#pragma unroll
+                for (int q = 0; q < 9; ++q) B[q] = Uk[q];
+            } else {
+                ld_mat<9>(B, uv, k - j, np, t, 9);
+            }
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc)
+                    P1[r * 3 + cc] += A[r * 3] * B[cc * 3] + A[r * 3 + 1] * B[cc * 3 + 1] +
+                                      A[r * 3 + 2] * B[cc * 3 + 2];
+        }
+        st_buf<9>(p0_slot(k), P0, np, t, 9);
+        st_buf<9>(p1_slot(k), P1, np, t, 9);
+    }
+}
+
 /*!
- * SVD-W.  Outputs (U, S, W).  Only the polar mode of the reference is lowered
- * (U and S have no readers; libsanm/oprs/linalg.cpp:529-550): hidden stack
- * P_k, self-bias cache = [D = Bm - Bp, Bpw] (18 doubles).
+ * SVD-W.  Outputs (U, S, W).  Polar mode (U and S have no readers;
+ * libsanm/oprs/linalg.cpp:529-550): hidden stack P_k, self-bias cache =
+ * [D = Bm - Bp, Bpw] (18 doubles).  Full mode (op.i[1]; U or S is read,
+ * linalg.cpp:551-563): the three outputs keep their stacks, hidden stack
+ * [P0_k = (U S)_k, P1_k = (U S U^T)_k] (18 doubles) makes the triple
+ * convolution of Mbias O(k), self-bias cache = [Bu, Bw, Mbias] (27 doubles).
  * aux0 = [U0 (9), S0 (3)].
  */
 SANM_HD inline void op_svdw(const DOp& op, const ItemCtx& c) {
@@ -1146,6 +1339,20 @@ SANM_HD inline void op_svdw(const DOp& op, const ItemCtx& c) {
         // eval_unary_func-style evaluation)
         st_buf<9>(c.var(op.out[0]).p0, U, np, t, 9);
         st_buf<3>(c.var(op.out[1]).p0, S, np, t, 3);
+        if (op.i[1] && op.auxk) {
+            double P0[9], P1[9];
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc) P0[r * 3 + cc] = U[r * 3 + cc] * S[cc];
+            mm3_nt(P1, P0, U);
+            st_buf<9>(op.auxk, P0, np, t, 9);
+            st_buf<9>(op.auxk + 9 * np, P1, np, t, 9);
+        }
+        return;
+    }
+    if (op.i[1]) {
+        op_svdw_full(op, c);
         return;
     }
     const int k = c.k;

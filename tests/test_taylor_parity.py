@@ -173,3 +173,26 @@ def test_batched_det_other_sizes(impl, ref, m):
         return x.batched_det() * x
 
     compare(impl, ref, build, xs, order)
+
+
+@pytest.mark.parametrize("require_rotation", [False, True])
+def test_svd_w_full_mode(impl, ref, require_rotation):
+    """BatchSVDW with U and S READ by the graph: the full mode of the
+    reference (libsanm/oprs/linalg.cpp:551-563, svd_w_taylor_fwd in
+    tensor_svd.cpp:275-387) instead of the polar mode `fea` uses.
+    y = (sum S) * U W^T - 2 W + U  exercises all three outputs."""
+    rng = np.random.default_rng(77)
+    n, order = 9, 8
+    xs = make_F_coeffs(rng, n, order, amp=0.05)
+    # distinct singular values (the U recurrence divides by S_i - S_j)
+    xs[0] = xs[0] * np.array([1.0, 1.3, 1.7])[None, None, :]
+
+    def build(g):
+        x = g.placeholder()
+        u, s, w = x.batched_svd_w(require_rotation)
+        tr = s.reduce_sum(1)  # [N, 1]
+        uwt = u.batched_matmul(w.batched_transpose())
+        return g.linear_combine([(1.0, tr * uwt), (-2.0, w), (1.0, u)], 0.0)
+
+    # (the U recurrence divides by S_i - S_j ~ 0.3: 5e-10 instead of 1e-10)
+    compare(impl, ref, build, xs, order, tol=5e-10)
