@@ -88,6 +88,20 @@ public:
     static std::unique_ptr<FusedKAssembly> build(
             const FusedIO& io, uint64_t n, const std::vector<uint32_t>& k_rowptr,
             const std::vector<uint32_t>& k_colidx);
+    //! the host half of build(): pure CPU work, no CUDA or profiler calls, so
+    //! that it can run on a helper thread beside the symbolic LU analysis
+    //! (both only need the K pattern); finish() uploads on the caller's thread
+    struct HostLists {
+        bool ok = false;
+        uint64_t n_tets = 0, nnz = 0, n = 0;
+        int64_t npad = 0;
+        std::vector<uint8_t> tab;
+        std::vector<uint32_t> kptr, ksrc;
+    };
+    static HostLists build_host(const FusedIO& io, uint64_t n,
+                                const std::vector<uint32_t>& k_rowptr,
+                                const std::vector<uint32_t>& k_colidx);
+    static std::unique_ptr<FusedKAssembly> finish(HostLists&& h);
     //! jac: [81][jac_pitch] (TaylorProp::ensure_jacobian of a fused graph)
     void assemble(double* vals, double* grad_t, const double* jac,
                   int64_t jac_pitch, const FusedIO& io) const;

@@ -97,11 +97,32 @@ struct GatherK {
 std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
         const FusedIO& io, uint64_t n, const std::vector<uint32_t>& k_rowptr,
         const std::vector<uint32_t>& k_colidx) {
+    return finish(build_host(io, n, k_rowptr, k_colidx));
+}
+
+std::unique_ptr<FusedKAssembly> FusedKAssembly::finish(HostLists&& h) {
+    if (!h.ok) return nullptr;
+    auto ret = std::unique_ptr<FusedKAssembly>(new FusedKAssembly);
+    ret->m_n_tets = h.n_tets;
+    ret->m_npad = h.npad;
+    ret->m_nnz = h.nnz;
+    ret->m_n = h.n;
+    ret->m_tab.upload(h.tab);
+    ret->m_kptr.upload(h.kptr);
+    ret->m_ksrc.upload(h.ksrc);
+    ret->m_cbuf.alloc((size_t)KE_ENTRIES * h.npad);
+    return ret;
+}
+
+FusedKAssembly::HostLists FusedKAssembly::build_host(
+        const FusedIO& io, uint64_t n, const std::vector<uint32_t>& k_rowptr,
+        const std::vector<uint32_t>& k_colidx) {
+    HostLists out;
     const uint64_t N = io.n_tets;
     const int64_t npad = io.npad;
-    if ((uint64_t)KE_ENTRIES * npad >= (1ull << 32)) return nullptr;
+    if ((uint64_t)KE_ENTRIES * npad >= (1ull << 32)) return out;
     const uint64_t nnz = k_rowptr[n];
-    if (nnz + n >= (1ull << 32) || io.nout != n) return nullptr;
+    if (nnz + n >= (1ull << 32) || io.nout != n) return out;
     const bool dbg = getenv("SANM_LU_DEBUG") != nullptr;
     auto tnow = [] { return std::chrono::steady_clock::now(); };
     auto t_start = tnow();
@@ -172,7 +193,7 @@ std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
         }
     }
     lap("dloc (parallel)");
-    if (bad) return nullptr;
+    if (bad) return out;
     // source lists per destination, ascending (tet, local entry): a counting
     // sort, parallel over destination ranges (every thread scans all of dloc
     // and keeps what falls into its range, so the order inside a list is the
@@ -208,17 +229,15 @@ std::unique_ptr<FusedKAssembly> FusedKAssembly::build(
         }
     }
     lap("fill");
-    auto ret = std::unique_ptr<FusedKAssembly>(new FusedKAssembly);
-    ret->m_n_tets = N;
-    ret->m_npad = npad;
-    ret->m_nnz = nnz;
-    ret->m_n = n;
-    ret->m_tab.upload(tab);
-    ret->m_kptr.upload(kptr);
-    ret->m_ksrc.upload(ksrc);
-    ret->m_cbuf.alloc((size_t)KE_ENTRIES * npad);
-    lap("upload");
-    return ret;
+    out.ok = true;
+    out.n_tets = N;
+    out.npad = npad;
+    out.nnz = nnz;
+    out.n = n;
+    out.tab = std::move(tab);
+    out.kptr = std::move(kptr);
+    out.ksrc = std::move(ksrc);
+    return out;
 }
 
 void FusedKAssembly::assemble(double* vals, double* grad_t, const double* jac,
