@@ -20,9 +20,15 @@
 
 namespace sanm_b200 {
 
+//! barrier of the 128 threads that run block_gj32 (a named barrier, so that
+//! the routine can also be called by the first four warps of a larger CTA)
+__device__ __forceinline__ void gj32_sync() {
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+}
+
 /*! D: shared, column-major, ld 32, rows/cols >= nb zero.  On return D holds
  * inv(P A) and lperm[i] = original row at position i.  acol: shared [64].
- * Must be called by all 128 threads of the CTA. */
+ * Must be called by threads 0..127 of the CTA, all of them. */
 __device__ inline void block_gj32(double* __restrict__ D, uint32_t nb,
                                   uint32_t* __restrict__ lperm,
                                   double* __restrict__ acol, double thresh,
@@ -32,7 +38,7 @@ __device__ inline void block_gj32(double* __restrict__ D, uint32_t nb,
     const uint32_t j0 = w * CW;
     uint32_t pos = lane;
     if (w == 0) acol[lane] = D[lane];  // column 0
-    __syncthreads();
+    gj32_sync();
     for (uint32_t k = 0; k < nb; ++k) {
         const bool eligible = pos >= k && pos < nb;
         const double a = acol[(k & 1) * NBK + lane];
@@ -77,19 +83,19 @@ __device__ inline void block_gj32(double* __restrict__ D, uint32_t nb,
             D[(j0 + j) * NBK + lane] = nv;
             if (j0 + j == k + 1) acol[((k + 1) & 1) * NBK + lane] = nv;
         }
-        __syncthreads();
+        gj32_sync();
     }
     // move the rows to their positions
     double r[CW];
 #pragma unroll
     for (int j = 0; j < CW; ++j) r[j] = D[(j0 + j) * NBK + lane];
-    __syncthreads();
+    gj32_sync();
     if (lane < nb) {
 #pragma unroll
         for (int j = 0; j < CW; ++j) D[(j0 + j) * NBK + pos] = r[j];
         if (w == 0) lperm[pos] = lane;
     }
-    __syncthreads();
+    gj32_sync();
 }
 
 }  // namespace sanm_b200

@@ -287,7 +287,7 @@ struct BigDiagKernel {
 #pragma unroll
             for (int j = 0; j < 8; ++j) D[(j0 + j) * NB + lane] = v[j];
             double* acol = reinterpret_cast<double*>(sh + 2);
-            __syncthreads();
+            gj32_sync();
             block_gj32(D, nb, lperm, acol, amax[0] * 1e-13, nr_perturbed);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {

@@ -242,8 +242,18 @@ SANM_HD inline void wide_clip(uint32_t a0, uint32_t a1, uint32_t t0, uint32_t* l
     }
 }
 
-//! D = (P_r F[P,P])^-1 in shared memory, one CTA per front; records the row
-//! permutation (lperm: position i of the block holds original row lperm[i])
+/*! D = (P_r F[P,P])^-1 in shared memory, one CTA per front; records the row
+ * permutation (lperm: position i of the block holds original row lperm[i]).
+ *
+ * CUDA build: blocked Gauss-Jordan inside shared memory, 32 pivots at a time:
+ * the 32 x 32 diagonal sub-block is inverted by the latency-tuned block_gj32
+ * (gj32.cuh, warps 0-3, partial pivoting inside the sub-block), then all 16
+ * warps apply it to the 128 x 128 block -- row panel R' = D_b (P R), rank-32
+ * update T -= C R' and column panel C' = -C D_b, each thread a 4 x 4 register
+ * block.  ~65 us per 128 pivots instead of ~390 us for the unblocked sweep
+ * (five block-wide barriers and a rank-1 update per pivot), which was 8 % of a
+ * large factorisation and kept fronts below 1024 rows off this path.
+ * Host-emulation build: the plain sweep (pivot search over the whole block). */
 struct WideDiagKernel {
     const FrontD* fronts;
     const uint32_t* list;
@@ -255,16 +265,119 @@ struct WideDiagKernel {
         if (kb >= f.nc) return;
         const uint32_t wb = f.nc - kb < (uint32_t)WB ? f.nc - kb : (uint32_t)WB;
         double* M = reinterpret_cast<double*>(c.smem);  // [wb][WB]
-        uint32_t* lperm = reinterpret_cast<uint32_t*>(M + (size_t)WB * WB);
-        int* sh = reinterpret_cast<int*>(lperm + WB);
         double* G = f.F + (uint64_t)kb * f.nr + kb;
         for (uint32_t e = c.tid; e < wb * wb; e += c.nthr) {
             const uint32_t i = e % wb, j = e / wb;
             M[j * WB + i] = G[(uint64_t)j * f.nr + i];
         }
+#ifdef SANM_HOSTEMU
+        uint32_t* lperm = reinterpret_cast<uint32_t*>(M + (size_t)WB * WB);
+        int* sh = reinterpret_cast<int*>(lperm + WB);
         for (uint32_t i = c.tid; i < wb; i += c.nthr) lperm[i] = i;
         c.sync();
         gj_steps(c, M, WB, wb, 0, wb, wb, lperm, sh, amax[0] * 1e-13, nr_perturbed);
+#else
+        constexpr int SB = 32;
+        double* D32 = M + (size_t)WB * WB;   // [32][32] inverted sub-block
+        double* Rb = D32 + SB * SB;          // [WB cols][32]: R'(m, j) at Rb[j * 32 + m]
+        double* Cb = Rb + (size_t)WB * SB;   // [32][WB rows]: C'(i, m) at Cb[m * WB + i]
+        double* acol = Cb + (size_t)WB * SB; // [64]
+        uint32_t* lp32 = reinterpret_cast<uint32_t*>(acol + 64);  // [32]
+        uint32_t* lperm = lp32 + SB;                              // [WB]
+        const double thresh = amax[0] * 1e-13;
+        const int tid = c.tid;
+        for (uint32_t o = 0; o < wb; o += SB) {
+            const uint32_t nb = wb - o < (uint32_t)SB ? wb - o : (uint32_t)SB;
+            __syncthreads();
+            if (tid < 128) {
+                // sub-block -> D32 (zero padded), inverted in place
+                const uint32_t lane = tid & 31, j0 = (tid >> 5) * 8;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    D32[(j0 + j) * SB + lane] =
+                            (lane < nb && j0 + j < nb) ? M[(o + j0 + j) * WB + o + lane] : 0.0;
+                }
+                gj32_sync();
+                block_gj32(D32, nb, lp32, acol, thresh, nr_perturbed);
+            }
+            __syncthreads();
+            // row panel: R'(m, j) = sum_q D32(m, q) M(o + lp32[q], j), j outside the sub-block
+            // 32 x wb outputs, each thread 4 rows (m) x 1 column
+            for (uint32_t e = tid; e < 8 * wb; e += c.nthr) {
+                const uint32_t j = e / 8, m4 = (e % 8) * 4;
+                double acc[4] = {0, 0, 0, 0};
+                if (j < o || j >= o + nb) {
+                    for (uint32_t q = 0; q < nb; ++q) {
+                        const double r = M[j * WB + o + lp32[q]];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) acc[u] += D32[q * SB + m4 + u] * r;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) Rb[j * SB + m4 + u] = acc[u];
+            }
+            // column panel: C'(i, m) = -sum_q M(i, o + q) D32(q, m), i outside the sub-block
+            for (uint32_t e = tid; e < 8 * wb; e += c.nthr) {
+                const uint32_t i = e % wb, m4 = (e / wb) * 4;
+                double acc[4] = {0, 0, 0, 0};
+                if (i < o || i >= o + nb) {
+                    for (uint32_t q = 0; q < nb; ++q) {
+                        const double cv = M[(o + q) * WB + i];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) acc[u] += cv * D32[(m4 + u) * SB + q];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) Cb[(m4 + u) * WB + i] = -acc[u];
+            }
+            __syncthreads();
+            // trailing update: M(i, j) -= sum_m M(i, o + m) R'(m, j), i and j outside;
+            // 4 x 4 register blocks over the wb x wb block
+            const uint32_t nt = (wb + 3) / 4;
+            for (uint32_t e = tid; e < nt * nt; e += c.nthr) {
+                const uint32_t i4 = (e % nt) * 4, j4 = (e / nt) * 4;
+                double acc[4][4] = {};
+                for (uint32_t m = 0; m < nb; ++m) {
+                    double a[4], b[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) a[u] = i4 + u < wb ? M[(o + m) * WB + i4 + u] : 0.0;
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) b[v] = j4 + v < wb ? Rb[(j4 + v) * SB + m] : 0.0;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+#pragma unroll
+                        for (int v = 0; v < 4; ++v) acc[u][v] += a[u] * b[v];
+                }
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const uint32_t j = j4 + v;
+                    if (j >= wb || (j >= o && j < o + nb)) continue;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t i = i4 + u;
+                        if (i >= wb || (i >= o && i < o + nb)) continue;
+                        M[j * WB + i] -= acc[u][v];
+                    }
+                }
+            }
+            __syncthreads();
+            // write the three finished pieces back into M
+            for (uint32_t e = tid; e < nb * wb; e += c.nthr) {
+                const uint32_t m = e % nb, j = e / nb;
+                if (j < o || j >= o + nb) {
+                    M[j * WB + o + m] = Rb[j * SB + m];
+                } else {
+                    M[j * WB + o + m] = D32[(j - o) * SB + m];
+                }
+            }
+            for (uint32_t e = tid; e < nb * wb; e += c.nthr) {
+                const uint32_t i = e % wb, m = e / wb;
+                if (i < o || i >= o + nb) M[(o + m) * WB + i] = Cb[m * WB + i];
+            }
+            if (tid < (int)nb) lperm[o + tid] = o + lp32[tid];
+        }
+        __syncthreads();
+#endif
         for (uint32_t e = c.tid; e < wb * wb; e += c.nthr) {
             const uint32_t i = e % wb, j = e / wb;
             G[(uint64_t)j * f.nr + i] = M[j * WB + i];
@@ -275,8 +388,14 @@ struct WideDiagKernel {
         }
     }
 };
+#ifdef SANM_HOSTEMU
 constexpr size_t W_DIAG_SMEM =
         (size_t)WB * WB * sizeof(double) + WB * sizeof(uint32_t) + 16;
+#else
+constexpr size_t W_DIAG_SMEM =
+        ((size_t)WB * WB + 32 * 32 + 2 * (size_t)WB * 32 + 64) * sizeof(double) +
+        (32 + WB) * sizeof(uint32_t);
+#endif
 
 //! ROW: R' = D (P_r R) on one 128-column tile; COL: C' = -C D on one 128-row tile
 template <bool ROW>
