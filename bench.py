@@ -887,7 +887,11 @@ def run_ours(args):
         # solver rooflines: back-solve bytes against the HBM peak,
         # factorisation flops against the DGEMM yardstick measured just now
         rl = []
-        for row in line["solves"]:
+        rows = list(line["solves"])
+        if big_row is not None and big_row.get("sparse"):
+            rows.append({"config": big_row["config"],
+                         "gpu": {"sparse": big_row["sparse"]}})
+        for row in rows:
             sp = row.get("gpu", {}).get("sparse")
             if not sp:
                 continue
