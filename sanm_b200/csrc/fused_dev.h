@@ -128,7 +128,8 @@ struct NHC {
     //! resident 128-thread blocks per SM the order-step kernel is compiled for
     //! (__launch_bounds__(128, MINB)); measured on B200, 2 M tets, K = 20:
     //! unbounded (ptxas picks 128 regs = 4 blocks) 2.43 G tet*order/s, 4: 2.43,
-    //! 5: 2.49, 6: 2.33 (spills)
+    //! 5: 2.49, 6: 2.33 (spills); with slot 0 reloaded per phase (fused.cu
+    //! load_base) 4: 2.37, 5: 2.56 (96 registers, no spill), 6: 2.52
     static constexpr int MINB = 5;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18 };
@@ -210,7 +211,8 @@ struct NHC {
  */
 struct NHI {
     static constexpr int S = 23;
-    //! unbounded (236 regs = 2 blocks) 1.61 G, 4: 1.85, 5: 1.61
+    //! unbounded (236 regs = 2 blocks) 1.61 G, 4: 1.85, 5: 1.61; with slot 0
+    //! reloaded per phase 4: 1.99 (128 registers, no spill), 5: 1.75, 6: 1.47
     static constexpr int MINB = 4;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18, oJ = 19, oQ = 20, oI = 21, oT = 22 };
@@ -329,8 +331,9 @@ struct NHI {
  */
 struct ARAP {
     static constexpr int S = 27;
-    //! unbounded (240 regs = 2 blocks) 1.43 G, 4: 1.56, 5: 1.55
-    static constexpr int MINB = 4;
+    //! unbounded (240 regs = 2 blocks) 1.43 G, 4: 1.56, 5: 1.55; with slot 0
+    //! reloaded per phase 4: 1.67, 5: 1.68, 6: 1.63
+    static constexpr int MINB = 5;
     static constexpr int AUX = 12;
     enum { oF = 0, oP = 9, oW = 18 };
     struct Acc {

@@ -880,6 +880,72 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         }
         sns.swap(kept);
     }
+    {
+        // Subtree collapse: a whole subtree of the supernodal tree whose
+        // columns (contiguous in the postorder) and the update rows of its root
+        // fit one small dense front becomes ONE leaf supernode.  The bottom of
+        // the tree (inside the nested-dissection leaves) is a forest of 1-20
+        // column supernodes several levels deep; every level costs the
+        // factorisation an assembly + a front launch and every solve two
+        // dependent launches, while the arithmetic of those fronts is
+        // negligible.  A collapsed front stays on the shared-memory path
+        // (sparse_lu.cu SMALL_NR).  Explicit zeros are bounded by the size cap.
+        static const u32 cap_nr = [] {
+            const char* e = getenv("SANM_LU_COLLAPSE_NR");
+            return e ? (u32)atoi(e) : 104u;
+        }();
+        static const u32 cap_nc = [] {
+            const char* e = getenv("SANM_LU_COLLAPSE_NC");
+            return e ? (u32)atoi(e) : 64u;
+        }();
+        const u32 m = (u32)sns.size();
+        if (cap_nr > 0 && m > 1) {
+            std::vector<u32> col2sn(n);
+            for (u32 s = 0; s < m; ++s) {
+                for (u32 c = 0; c < sns[s].nc; ++c) col2sn[sns[s].c0 + c] = s;
+            }
+            std::vector<int32_t> par(m, -1);
+            std::vector<u32> first(m);
+            for (u32 s = 0; s < m; ++s) {
+                first[s] = sns[s].c0;
+                const int32_t pc = parent[sns[s].c0 + sns[s].nc - 1];
+                if (pc >= 0) par[s] = (int32_t)col2sn[pc];
+            }
+            // children precede parents in the postorder
+            for (u32 s = 0; s < m; ++s) {
+                if (par[s] >= 0) first[par[s]] = std::min(first[par[s]], first[s]);
+            }
+            auto fits = [&](u32 s) {
+                const u64 sub_nc = (u64)sns[s].c0 + sns[s].nc - first[s];
+                const u64 nr2 = sub_nc + (sns[s].nr - sns[s].nc);
+                return sub_nc <= cap_nc && nr2 <= cap_nr;
+            };
+            // descending: a root is met before the members of its subtree,
+            // which are exactly the records starting at or after its first column
+            std::vector<SN> kept;
+            u32 cur_first = n;
+            for (u32 s = m; s-- > 0;) {
+                if (sns[s].c0 >= cur_first) continue;  // inside a collapsed subtree
+                if (fits(s) && first[s] < sns[s].c0) {
+                    const u32 sub_nc = sns[s].c0 + sns[s].nc - first[s];
+                    kept.push_back({first[s], sub_nc, sub_nc + (sns[s].nr - sns[s].nc)});
+                    cur_first = first[s];
+                } else {
+                    kept.push_back(sns[s]);
+                }
+            }
+            std::reverse(kept.begin(), kept.end());
+            // a subtree is a contiguous column range ending at its root, so the
+            // records that survive still tile [0, n) in order
+            u32 at = 0;
+            for (const SN& k : kept) {
+                sanm_check(k.c0 == at, "subtree collapse broke the column tiling");
+                at += k.nc;
+            }
+            sanm_check(at == n);
+            sns.swap(kept);
+        }
+    }
     const u32 nsn = (u32)sns.size();
     S.nsn = nsn;
     S.sn_c0.resize(nsn);
