@@ -29,7 +29,15 @@ struct LuScope {
 };
 
 constexpr int NB = 32;          //!< pivot block of the large-front path
-constexpr uint32_t SMALL_NR = 104;  //!< fronts up to this size live in smem
+//! fronts up to this size are factored inside shared memory by one CTA
+//! (104^2 doubles = 86 KB: two CTAs per SM; at most 168 fits the 227 KB limit)
+uint32_t small_nr() {
+    static const uint32_t v = [] {
+        const char* e = getenv("SANM_LU_SMALL_NR");
+        return e ? (uint32_t)std::min(168, std::max(32, atoi(e))) : 104u;
+    }();
+    return v;
+}
 constexpr int ASM_TILE = 4096;  //!< entries per assembly task
 constexpr int ABSMAX_BLOCKS = 256;
 constexpr int LPERM_PER_FRONT = 128;  //!< >= 2 * NB (narrow path) and >= WB (wide path)
@@ -319,6 +327,44 @@ struct BigDiagKernel {
     }
 };
 
+/* The tile kernels of the narrow path run one wave of 64 x 64 tiles per launch
+ * on the top fronts, two warps per scheduler: what a launch costs is the
+ * number of instructions a warp executes, not bandwidth (ncu on a 121-tile
+ * launch: 12 cycles per issued instruction, two thirds of the samples in the
+ * index arithmetic and predicates of the tile fills and of the epilogue).  So
+ * the tiles have compile-time shapes: fills map element -> (row, column) with
+ * shifts, every load of a thread is issued before its first shared-memory
+ * store, entries outside the front or past the last pivot are ZERO so that the
+ * product loops run a fixed NB iterations, and the pivot rows / columns are
+ * masked once per thread. */
+#ifdef SANM_HOSTEMU
+#define SANM_TILE_THREADS(c) ((uint32_t)(c).nthr)
+#else
+#define SANM_TILE_THREADS(c) 256u
+#endif
+
+//! dst[e] = src(e) (address or null -> 0) for e < TOTAL; CUDA: 256 threads,
+//! TOTAL / 256 loads in flight per thread (read-only path)
+template <int TOTAL, class Src>
+SANM_D inline void stage_fixed(const rt::BlockCtx& c, double* dst, Src src) {
+#ifdef SANM_HOSTEMU
+    for (uint32_t e = c.tid; e < (uint32_t)TOTAL; e += c.nthr) {
+        const double* p = src(e);
+        dst[e] = p ? *p : 0.0;
+    }
+#else
+    constexpr int PER = TOTAL / 256;
+    double r[PER];
+#pragma unroll
+    for (int it = 0; it < PER; ++it) {
+        const double* p = src((uint32_t)c.tid + it * 256);
+        r[it] = p ? SANM_LDG(p) : 0.0;
+    }
+#pragma unroll
+    for (int it = 0; it < PER; ++it) dst[c.tid + it * 256] = r[it];
+#endif
+}
+
 //! R' = Dinv * R for a tile of 64 columns outside the pivot block
 struct BigRowPanelKernel {
     const FrontD* fronts;
@@ -330,29 +376,30 @@ struct BigRowPanelKernel {
         const uint32_t tile = (uint32_t)(c.bid % tiles);
         if (kb >= f.nc || tile * 64 >= f.nr) return;
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
-        double* Di = reinterpret_cast<double*>(c.smem);  // [NB*NB]
-        double* R = Di + NB * NB;                        // [NB*64]
+        double* Di = reinterpret_cast<double*>(c.smem);  // [NB][NB] : Di[m*NB+i]
+        double* R = Di + NB * NB;                        // [64][NB] : R[j*NB+m]
         const uint32_t j0 = tile * 64;
         const uint32_t nj = f.nr - j0 < 64 ? f.nr - j0 : 64;
-        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
-            uint32_t i = e % nb, j = e / nb;
-            Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
-        }
         // rows of the pivot block were swapped by BigDiagKernel (lperm)
         const uint32_t* lp = f.lperm + ((kb / NB) & 1) * NB;
-        for (uint32_t e = c.tid; e < nb * nj; e += c.nthr) {
-            uint32_t i = e % nb, j = e / nb;
-            R[j * NB + i] = f.F[(uint64_t)(j0 + j) * f.nr + kb + lp[i]];
-        }
+        const double* Fk = f.F + kb;
+        stage_fixed<NB * NB>(c, Di, [&](uint32_t e) -> const double* {
+            const uint32_t i = e % NB, m = e / NB;
+            return i < nb && m < nb ? Fk + (uint64_t)(kb + m) * f.nr + i : nullptr;
+        });
+        stage_fixed<NB * 64>(c, R, [&](uint32_t e) -> const double* {
+            const uint32_t m = e % NB, j = e / NB;
+            return m < nb && j < nj ? Fk + (uint64_t)(j0 + j) * f.nr + lp[m] : nullptr;
+        });
         c.sync();
         // 4 rows x 2 columns per thread (8 x 32 thread grid in the CUDA build):
         // 8 FMAs per 6 shared loads instead of 1 per 2 -- the plain dot-product
-        // form is bound by shared-memory bandwidth.  Entries past nb / nj are
-        // computed from stale shared memory and never stored.
-        for (uint32_t q = c.tid; q < 256; q += c.nthr) {
+        // form is bound by shared-memory bandwidth
+        for (uint32_t q = c.tid; q < 256; q += SANM_TILE_THREADS(c)) {
             const uint32_t i4 = (q % 8) * 4, j2 = (q / 8) * 2;
             double acc[4][2] = {};
-            for (uint32_t m = 0; m < nb; ++m) {
+#pragma unroll 8
+            for (uint32_t m = 0; m < (uint32_t)NB; ++m) {
                 double a[4], b[2];
                 for (int u = 0; u < 4; ++u) a[u] = Di[m * NB + i4 + u];
                 for (int v = 0; v < 2; ++v) b[v] = R[(j2 + v) * NB + m];
@@ -391,30 +438,50 @@ struct BigGemmKernel {
         double* Cs = reinterpret_cast<double*>(c.smem);  // [NB][64] : Cs[m*64+i]
         double* Rs = Cs + NB * 64;                       // [64][NB] : Rs[j*NB+m]
         double* Rr = Rs + NB * 64;                       // [64][NB] : R before Dinv
-        double* Di = Rr + NB * 64;                       // [NB*NB]
+        double* Di = Rr + NB * 64;                       // [NB][NB] : Di[m*NB+i]
         const uint32_t* lp = f.lperm + ((kb / NB) & 1) * NB;
         const uint32_t i0 = ti * 64, j0 = tj * 64;
         const uint32_t ni = f.nr - i0 < 64 ? f.nr - i0 : 64;
         const uint32_t nj = f.nr - j0 < 64 ? f.nr - j0 : 64;
-        for (uint32_t e = c.tid; e < nb * 64; e += c.nthr) {
-            uint32_t i = e % 64, m = e / 64;
-            Cs[m * 64 + i] = i < ni ? f.F[(uint64_t)(kb + m) * f.nr + i0 + i] : 0.0;
-        }
-        for (uint32_t e = c.tid; e < nb * 64; e += c.nthr) {
-            uint32_t m = e % nb, j = e / nb;
-            Rr[j * NB + m] = j < nj ? f.F[(uint64_t)(j0 + j) * f.nr + kb + lp[m]] : 0.0;
-        }
-        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
-            uint32_t i = e % nb, j = e / nb;
-            Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
-        }
+        // local rows / columns that belong to the pivot block of this step
+        const uint32_t pr0 = kb > i0 ? kb - i0 : 0, pr1 = kb + nb > i0 ? kb + nb - i0 : 0;
+        const uint32_t pc0 = kb > j0 ? kb - j0 : 0, pc1 = kb + nb > j0 ? kb + nb - j0 : 0;
+        auto row_ok = [&](uint32_t li) { return li < ni && !(li >= pr0 && li < pr1); };
+        auto col_ok = [&](uint32_t lj) { return lj < nj && !(lj >= pc0 && lj < pc1); };
+        // The accumulators start from the tile itself (T - C R' instead of a
+        // read-modify-write epilogue of 16 dependent round trips per thread)
+        double* T0 = f.F + (uint64_t)j0 * f.nr + i0;
+        auto load_tile = [&](double (*acc)[4], uint32_t q) {
+            const uint32_t qi = (q % 16) * 4, qj = (q / 16) * 4;
+            for (int v = 0; v < 4; ++v)
+                for (int u = 0; u < 4; ++u)
+                    acc[u][v] = row_ok(qi + u) && col_ok(qj + v)
+                                        ? T0[(uint64_t)(qj + v) * f.nr + qi + u]
+                                        : 0.0;
+        };
+        double tacc[4][4];
+        const bool early = SANM_TILE_THREADS(c) >= 256;  // one 4 x 4 block per thread
+        if (early) load_tile(tacc, c.tid);
+        const double* Fk = f.F + kb;
+        stage_fixed<NB * 64>(c, Cs, [&](uint32_t e) -> const double* {
+            const uint32_t i = e % 64, m = e / 64;
+            return i < ni && m < nb ? f.F + (uint64_t)(kb + m) * f.nr + i0 + i : nullptr;
+        });
+        stage_fixed<NB * 64>(c, Rr, [&](uint32_t e) -> const double* {
+            const uint32_t m = e % NB, j = e / NB;
+            return m < nb && j < nj ? Fk + (uint64_t)(j0 + j) * f.nr + lp[m] : nullptr;
+        });
+        stage_fixed<NB * NB>(c, Di, [&](uint32_t e) -> const double* {
+            const uint32_t i = e % NB, m = e / NB;
+            return i < nb && m < nb ? Fk + (uint64_t)(kb + m) * f.nr + i : nullptr;
+        });
         c.sync();
-        // same operation order as BigRowPanelKernel; rows past nb come from
-        // stale shared memory and are never read
-        for (uint32_t q = c.tid; q < 256; q += c.nthr) {
+        // same operation order as BigRowPanelKernel
+        for (uint32_t q = c.tid; q < 256; q += SANM_TILE_THREADS(c)) {
             const uint32_t i4 = (q % 8) * 4, j2 = (q / 8) * 2;
             double acc[4][2] = {};
-            for (uint32_t m = 0; m < nb; ++m) {
+#pragma unroll 8
+            for (uint32_t m = 0; m < (uint32_t)NB; ++m) {
                 double a[4], b[2];
                 for (int u = 0; u < 4; ++u) a[u] = Di[m * NB + i4 + u];
                 for (int v = 0; v < 2; ++v) b[v] = Rr[(j2 + v) * NB + m];
@@ -427,23 +494,25 @@ struct BigGemmKernel {
         c.sync();
         // 16 x 16 thread grid in the CUDA build (256 threads), 4x4 per thread;
         // generic strided form so that the host build (1 thread) is the same code
-        for (uint32_t q = c.tid; q < 256; q += c.nthr) {
+        for (uint32_t q = c.tid; q < 256; q += SANM_TILE_THREADS(c)) {
             const uint32_t qi = (q % 16) * 4, qj = (q / 16) * 4;
-            double acc[4][4] = {};
-            for (uint32_t m = 0; m < nb; ++m) {
+            if (!early) load_tile(tacc, q);
+#pragma unroll 8
+            for (uint32_t m = 0; m < (uint32_t)NB; ++m) {
                 double a[4], b[4];
                 for (int u = 0; u < 4; ++u) a[u] = Cs[m * 64 + qi + u];
                 for (int u = 0; u < 4; ++u) b[u] = Rs[(qj + u) * NB + m];
                 for (int u = 0; u < 4; ++u)
-                    for (int v = 0; v < 4; ++v) acc[u][v] += a[u] * b[v];
+                    for (int v = 0; v < 4; ++v) tacc[u][v] -= a[u] * b[v];
             }
+            bool ro[4], co[4];
+            for (int u = 0; u < 4; ++u) ro[u] = row_ok(qi + u);
+            for (int v = 0; v < 4; ++v) co[v] = col_ok(qj + v);
             for (int v = 0; v < 4; ++v) {
-                const uint32_t gj = j0 + qj + v;
-                if (qj + v >= nj || (gj >= kb && gj < kb + nb)) continue;
+                if (!co[v]) continue;
+                double* col = T0 + (uint64_t)(qj + v) * f.nr + qi;
                 for (int u = 0; u < 4; ++u) {
-                    const uint32_t gi = i0 + qi + u;
-                    if (qi + u >= ni || (gi >= kb && gi < kb + nb)) continue;
-                    f.F[(uint64_t)gj * f.nr + gi] -= acc[u][v];
+                    if (ro[u]) col[u] = tacc[u][v];
                 }
             }
         }
@@ -461,24 +530,25 @@ struct BigColPanelKernel {
         const uint32_t tile = (uint32_t)(c.bid % tiles);
         if (kb >= f.nc || tile * 64 >= f.nr) return;
         const uint32_t nb = f.nc - kb < (uint32_t)NB ? f.nc - kb : (uint32_t)NB;
-        double* Di = reinterpret_cast<double*>(c.smem);  // [NB*NB]
-        double* Cs = Di + NB * NB;                       // [NB][64]
+        double* Di = reinterpret_cast<double*>(c.smem);  // [NB][NB] : Di[q*NB+m]
+        double* Cs = Di + NB * NB;                       // [NB][64] : Cs[m*64+i]
         const uint32_t i0 = tile * 64;
         const uint32_t ni = f.nr - i0 < 64 ? f.nr - i0 : 64;
-        for (uint32_t e = c.tid; e < nb * nb; e += c.nthr) {
-            uint32_t i = e % nb, j = e / nb;
-            Di[j * NB + i] = f.F[(uint64_t)(kb + j) * f.nr + kb + i];
-        }
-        for (uint32_t e = c.tid; e < nb * ni; e += c.nthr) {
-            uint32_t i = e % ni, m = e / ni;
-            Cs[m * 64 + i] = f.F[(uint64_t)(kb + m) * f.nr + i0 + i];
-        }
+        stage_fixed<NB * NB>(c, Di, [&](uint32_t e) -> const double* {
+            const uint32_t i = e % NB, j = e / NB;
+            return i < nb && j < nb ? f.F + (uint64_t)(kb + j) * f.nr + kb + i : nullptr;
+        });
+        stage_fixed<NB * 64>(c, Cs, [&](uint32_t e) -> const double* {
+            const uint32_t i = e % 64, m = e / 64;
+            return i < ni && m < nb ? f.F + (uint64_t)(kb + m) * f.nr + i0 + i : nullptr;
+        });
         c.sync();
         // 4 rows x 2 columns per thread (16 x 16 thread grid), see the row panel
-        for (uint32_t t = c.tid; t < 256; t += c.nthr) {
+        for (uint32_t t = c.tid; t < 256; t += SANM_TILE_THREADS(c)) {
             const uint32_t i4 = (t % 16) * 4, q2 = (t / 16) * 2;
             double acc[4][2] = {};
-            for (uint32_t m = 0; m < nb; ++m) {
+#pragma unroll 8
+            for (uint32_t m = 0; m < (uint32_t)NB; ++m) {
                 double a[4], b[2];
                 for (int u = 0; u < 4; ++u) a[u] = Cs[m * 64 + i4 + u];
                 for (int v = 0; v < 2; ++v) b[v] = Di[(q2 + v) * NB + m];
@@ -560,14 +630,36 @@ constexpr int FWD_ROWS = 32, FWD_GROUPS_NARROW = 8, FWD_GROUPS_WIDE = 32;
 constexpr uint32_t SOLVE_WIDE_COLS = 192;
 constexpr int SOLVE_STAGE = 8;  //!< partials summed per thread in stage 1
 
-//! partial dot product of one row of a column-major block with v
+//! first batch of solve_partial's factor loads (columns g, g + GROUPS, ...):
+//! issued by the kernels' pre-wait prologues
+template <int GROUPS>
+SANM_HD inline void solve_prefetch(double* a, const double* __restrict__ col0,
+                                   uint64_t ld, uint32_t ncol, int g) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const uint32_t jj = g + u * GROUPS;
+        a[u] = jj < ncol ? SANM_LDG(col0 + (uint64_t)jj * ld) : 0.0;
+    }
+}
+
+//! partial dot product of one row of a column-major block with v; a0 (or
+//! null) = the first batch of factor entries, already loaded by solve_prefetch
 template <int GROUPS>
 SANM_HD inline double solve_partial(const double* __restrict__ col0, uint64_t ld,
                                     uint32_t ncol, const double* __restrict__ v,
-                                    int g) {
+                                    int g, const double* a0 = nullptr) {
     constexpr int U = 8;
     double acc[U] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (uint32_t j = g; j < ncol; j += U * GROUPS) {
+    uint32_t j = g;
+    if (a0 && j < ncol) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t jj = j + u * GROUPS;
+            acc[u] += a0[u] * (jj < ncol ? v[jj] : 0.0);
+        }
+        j += U * GROUPS;
+    }
+    for (; j < ncol; j += U * GROUPS) {
         double a[U], x[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -616,10 +708,50 @@ constexpr size_t solve_scratch_doubles() {
     return (size_t)SOLVE_ROWS * GROUPS + (size_t)SOLVE_ROWS * (GROUPS / SOLVE_STAGE);
 }
 
+/*! A gathered sum  base + sum_p vecs[gsrc[p]]  whose index loads were issued
+ * before the kernel's dependency wait: the first two sources (a front rarely
+ * has more than two children touching a row), the rest as a range. */
+struct GatherIdx {
+    uint32_t s0, s1, rest0, rest1;
+};
+constexpr uint32_t NO_SRC = 0xFFFFFFFFu;
+SANM_HD inline GatherIdx gather_idx(const uint32_t* __restrict__ gptr,
+                                    const uint32_t* __restrict__ gsrc, uint32_t row) {
+    GatherIdx g;
+    const uint32_t p0 = gptr[row], p1 = gptr[row + 1];
+    g.s0 = p0 < p1 ? gsrc[p0] : NO_SRC;
+    g.s1 = p0 + 1 < p1 ? gsrc[p0 + 1] : NO_SRC;
+    g.rest0 = p0 + 2 < p1 ? p0 + 2 : p1;
+    g.rest1 = p1;
+    return g;
+}
+//! same summation order as the plain loop (child order)
+SANM_HD inline double gather_sum(double base, const GatherIdx& g,
+                                 const uint32_t* __restrict__ gsrc,
+                                 const double* vecs) {
+    // both loads in flight together
+    const double c0 = vecs[g.s0 != NO_SRC ? g.s0 : 0];
+    const double c1 = vecs[g.s1 != NO_SRC ? g.s1 : 0];
+    double v = base;
+    if (g.s0 != NO_SRC) v += c0;
+    if (g.s1 != NO_SRC) v += c1;
+    for (uint32_t p = g.rest0; p < g.rest1; ++p) v += vecs[gsrc[p]];
+    return v;
+}
+
 //! forward: vec = [w1' ; w2 + F21' w1'] with w = b + gathered child updates;
 //! b is read through the fill-reducing permutation
 //! VG: the front's w1' was written to f.vec[0 .. nc) by SolvePrepKernel and is
 //! read from global memory (fronts too large for a shared-memory copy)
+//!
+//! hoist: everything that does not depend on the level below -- index lists,
+//! the row permutation, b, and the first batch of the thread's factor row --
+//! is loaded in pre(), i.e. before griddepcontrol.wait, while the previous
+//! level is still computing; what remains after the wait is one round trip for
+//! the child updates, the shared-memory permutation and the reduction.  Only
+//! data written at least two kernels earlier may be hoisted (a kernel's
+//! prologue can overlap its predecessor, whose own wait guarantees everything
+//! before it): the first launch of a sweep runs with hoist = 0.
 template <int SOLVE_ROWS, int GROUPS, bool VG = false>
 struct ForwardKernel {
     static constexpr int SOLVE_THREADS = SOLVE_ROWS * GROUPS;
@@ -629,56 +761,95 @@ struct ForwardKernel {
     const Task* tasks;
     const double* b;       // right-hand side, original numbering
     const uint32_t* perm;  // new index -> original index
+    int hoist;
     struct Pre {
         Task tk;
         FrontD f;
+        GatherIdx gw, gt;  //!< w1 row tid; update row r0 + tid (tid < SOLVE_ROWS)
+        double bv;
+        uint32_t rp;
+        double a[8];
     };
-    //! descriptors only (rt.h HasPre)
     SANM_D Pre pre(const rt::BlockCtx& c) const {
         Pre p;
         p.tk = tasks[c.bid];
         p.f = fronts[p.tk.front];
+        if (!VG && hoist) {
+            const FrontD& f = p.f;
+            const uint32_t i = c.tid;
+            if (i < f.nc) {
+                p.gw = gather_idx(f.gptr, gsrc, i);
+                p.bv = b[perm[f.c0 + i]];
+                p.rp = f.rowperm[i];
+            }
+            const uint32_t nu = f.nr - f.nc, r0 = p.tk.chunk * SOLVE_ROWS;
+            if (c.tid < SOLVE_ROWS && r0 + c.tid < nu) {
+                p.gt = gather_idx(f.gptr, gsrc, f.nc + r0 + c.tid);
+            }
+            if (c.tid < SOLVE_THREADS) {
+                const int lane = c.tid % SOLVE_ROWS, g = c.tid / SOLVE_ROWS;
+                if (r0 + lane < nu) {
+                    solve_prefetch<GROUPS>(p.a, f.F + f.nc + r0 + lane, f.nr, f.nc, g);
+                }
+            }
+        }
         return p;
     }
     SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
     SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
         const Task tk = p.tk;
         const FrontD& f = p.f;
+        const bool h = !VG && hoist;
         double* w1 = reinterpret_cast<double*>(c.smem);
         const double* w1p = VG ? f.vec : w1 + f.nc;
         double* part = VG ? w1 : w1 + 2 * (size_t)f.nc;
+        const uint32_t nu = f.nr - f.nc;
+        const uint32_t r0 = tk.chunk * SOLVE_ROWS;
+        // the update rows' child contributions do not depend on this front's
+        // product: gathered up front, beside the w1 gather
+        double tail = 0;
+        if (h && c.tid < SOLVE_ROWS && r0 + c.tid < nu) {
+            tail = gather_sum(0.0, p.gt, gsrc, vecs);
+        }
         if (!VG) {
             double* w1p_s = w1 + f.nc;
             for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
                 // child updates in child order (flattened at analysis time:
                 // offsets into the work vectors), so the sum is the one of the
                 // tree walk
-                double v = b[perm[f.c0 + i]];
-                for (uint32_t p = f.gptr[i], pe = f.gptr[i + 1]; p < pe; ++p) v += vecs[gsrc[p]];
-                w1[i] = v;
+                if (h && i == (uint32_t)c.tid) {
+                    w1[i] = gather_sum(p.bv, p.gw, gsrc, vecs);
+                } else {
+                    double v = b[perm[f.c0 + i]];
+                    for (uint32_t q = f.gptr[i], qe = f.gptr[i + 1]; q < qe; ++q) v += vecs[gsrc[q]];
+                    w1[i] = v;
+                }
             }
             c.sync();
             for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
-                w1p_s[i] = w1[f.rowperm[i]];
+                const uint32_t rp = (h && i == (uint32_t)c.tid) ? p.rp : f.rowperm[i];
+                w1p_s[i] = w1[rp];
                 if (tk.chunk == 0) f.vec[i] = w1p_s[i];
             }
             c.sync();
         }
-        const uint32_t nu = f.nr - f.nc;
-        const uint32_t r0 = tk.chunk * SOLVE_ROWS;
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
             const uint32_t r = r0 + lane;
-            part[th] = r < nu ? solve_partial<GROUPS>(f.F + f.nc + r, f.nr, f.nc, w1p, g)
+            part[th] = r < nu ? solve_partial<GROUPS>(f.F + f.nc + r, f.nr, f.nc, w1p, g,
+                                                      h && th == c.tid ? p.a : nullptr)
                               : 0.0;
         }
         solve_reduce<SOLVE_ROWS, GROUPS>(c, part);
         for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
             const uint32_t r = r0 + lane;
             if (r >= nu) continue;
-            double acc = 0;
-            for (uint32_t p = f.gptr[f.nc + r], pe = f.gptr[f.nc + r + 1]; p < pe; ++p) {
-                acc += vecs[gsrc[p]];
+            double acc = tail;
+            if (!(h && lane == c.tid)) {
+                acc = 0;
+                for (uint32_t q = f.gptr[f.nc + r], qe = f.gptr[f.nc + r + 1]; q < qe; ++q) {
+                    acc += vecs[gsrc[q]];
+                }
             }
             f.vec[f.nc + r] = acc + part[lane];
         }
@@ -689,6 +860,8 @@ struct ForwardKernel {
 //! by descendants) and to the caller's vector in original numbering
 //! VG: [w1' ; -x2] is f.vec (the tail written by SolvePrepKernel), read from
 //! global memory
+//! hoist: see ForwardKernel; after the wait only x2 (the ancestors' solution)
+//! is fetched
 template <int SOLVE_ROWS, int GROUPS, bool VG = false>
 struct BackwardKernel {
     static constexpr int SOLVE_THREADS = SOLVE_ROWS * GROUPS;
@@ -697,34 +870,59 @@ struct BackwardKernel {
     double* xp;  // permuted solution
     double* x;   // solution, original numbering
     const uint32_t* perm;
+    int hoist;
     struct Pre {
         Task tk;
         FrontD f;
+        double w;          //!< f.vec[tid] (tid < nc)
+        uint32_t sti;      //!< f.st[nc + tid]
+        uint32_t pm;       //!< perm[c0 + r0 + tid] (tid < SOLVE_ROWS)
+        double a[8];
     };
-    //! descriptors only (rt.h HasPre)
     SANM_D Pre pre(const rt::BlockCtx& c) const {
         Pre p;
         p.tk = tasks[c.bid];
         p.f = fronts[p.tk.front];
+        if (!VG && hoist) {
+            const FrontD& f = p.f;
+            const uint32_t i = c.tid, r0 = p.tk.chunk * SOLVE_ROWS;
+            if (i < f.nc) p.w = f.vec[i];
+            if (f.nc + i < f.nr) p.sti = f.st[f.nc + i];
+            if (c.tid < SOLVE_ROWS && r0 + i < f.nc) p.pm = perm[f.c0 + r0 + i];
+            if (c.tid < SOLVE_THREADS) {
+                const int lane = c.tid % SOLVE_ROWS, g = c.tid / SOLVE_ROWS;
+                if (r0 + lane < f.nc) {
+                    solve_prefetch<GROUPS>(p.a, f.F + r0 + lane, f.nr, f.nr, g);
+                }
+            }
+        }
         return p;
     }
     SANM_D void operator()(const rt::BlockCtx& c) const { (*this)(c, pre(c)); }
     SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
         const Task tk = p.tk;
         const FrontD& f = p.f;
+        const bool h = !VG && hoist;
         double* vs = reinterpret_cast<double*>(c.smem);  // [w1' ; -x2]
         const double* v = VG ? f.vec : vs;
         double* part = VG ? vs : vs + f.nr;
         if (!VG) {
-            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) vs[i] = f.vec[i];
-            for (uint32_t i = f.nc + c.tid; i < f.nr; i += c.nthr) vs[i] = -xp[f.st[i]];
+            for (uint32_t i = c.tid; i < f.nc; i += c.nthr) {
+                vs[i] = (h && i == (uint32_t)c.tid) ? p.w : f.vec[i];
+            }
+            for (uint32_t i = f.nc + c.tid; i < f.nr; i += c.nthr) {
+                const uint32_t sti = (h && i == f.nc + c.tid) ? p.sti : f.st[i];
+                vs[i] = -xp[sti];
+            }
             c.sync();
         }
         const uint32_t r0 = tk.chunk * SOLVE_ROWS;
         for (int th = c.tid; th < SOLVE_THREADS; th += c.nthr) {
             const int lane = th % SOLVE_ROWS, g = th / SOLVE_ROWS;
             const uint32_t r = r0 + lane;
-            part[th] = r < f.nc ? solve_partial<GROUPS>(f.F + r, f.nr, f.nr, v, g) : 0.0;
+            part[th] = r < f.nc ? solve_partial<GROUPS>(f.F + r, f.nr, f.nr, v, g,
+                                                        h && th == c.tid ? p.a : nullptr)
+                                : 0.0;
         }
         solve_reduce<SOLVE_ROWS, GROUPS>(c, part);
         for (int lane = c.tid; lane < SOLVE_ROWS; lane += c.nthr) {
@@ -732,7 +930,7 @@ struct BackwardKernel {
             if (r >= f.nc) continue;
             const double acc = part[lane];
             xp[f.c0 + r] = acc;
-            x[perm[f.c0 + r]] = acc;
+            x[(h && lane == c.tid) ? p.pm : perm[f.c0 + r]] = acc;
         }
     }
 };
@@ -809,10 +1007,10 @@ struct SolvePhased {
                 c2.bid = t;
                 if (L.fwd_wide) {
                     ForwardKernel<FWD_ROWS, FWD_GROUPS_WIDE>{
-                            fronts, gsrc, vecs, fwd_tasks + L.fwd_off, b, perm}(c2);
+                            fronts, gsrc, vecs, fwd_tasks + L.fwd_off, b, perm, 1}(c2);
                 } else {
                     ForwardKernel<FWD_ROWS, FWD_GROUPS_NARROW>{
-                            fronts, gsrc, vecs, fwd_tasks + L.fwd_off, b, perm}(c2);
+                            fronts, gsrc, vecs, fwd_tasks + L.fwd_off, b, perm, 1}(c2);
                 }
                 c.sync();  // shared memory is reused by the next task
             }
@@ -822,10 +1020,10 @@ struct SolvePhased {
                 c2.bid = t;
                 if (L.bwd_wide) {
                     BackwardKernel<BWD_ROWS, BWD_GROUPS_WIDE>{
-                            fronts, bwd_tasks + L.bwd_off, xp, x, perm}(c2);
+                            fronts, bwd_tasks + L.bwd_off, xp, x, perm, 1}(c2);
                 } else {
                     BackwardKernel<BWD_ROWS, BWD_GROUPS_NARROW>{
-                            fronts, bwd_tasks + L.bwd_off, xp, x, perm}(c2);
+                            fronts, bwd_tasks + L.bwd_off, xp, x, perm, 1}(c2);
                 }
                 c.sync();
             }
@@ -891,6 +1089,7 @@ struct SparseLU::Impl {
     rt::DBuf<FrontD> fd;
     bool factored = false;
     bool counters_read = false;
+    bool bench_done = false;
     rt::DBuf<double> ref_b, ref_r, ref_dx;  //!< iterative refinement (on demand)
 };
 
@@ -1040,7 +1239,7 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                     asm_t.push_back({s, (uint32_t)t});
                 }
             }
-            if (nr <= SMALL_NR) {
+            if (nr <= small_nr()) {
                 small_l.push_back(s);
                 L.small_max_nr = std::max(L.small_max_nr, nr);
             } else if (nr >= wide_min) {
@@ -1218,7 +1417,9 @@ void SparseLU::factor(const double* vals_dev) {
             for (uint32_t kb = 0; kb < L.big_max_nc; kb += NB) {
                 {
                     LuScope ps{"lu_gemm"};
-                    rt::for_each_block<256>((size_t)L.big_n * tiles * tiles, 256,
+                    // two CTAs per SM (128 registers): a front of 700 rows is
+                    // 121 tiles, a level several of them
+                    rt::for_each_block<256, 2>((size_t)L.big_n * tiles * tiles, 256,
                                        (3 * NB * 64 + NB * NB) * sizeof(double),
                                        BigGemmKernel{I.fd.ptr(), list, kb, tiles});
                 }
@@ -1263,6 +1464,48 @@ struct AxpyKernel {
 void SparseLU::solve(double* x_dev, const double* b_dev) {
     Impl& I = *m_impl;
     sanm_check(I.factored, "solve() before factor()");
+#ifndef SANM_HOSTEMU
+    if (getenv("SANM_LU_SOLVE_BENCH") && !I.bench_done) {
+        // diagnostic: is a solve bound by the host's launch rate or by the
+        // device?  20 solves enqueued back to back (host time to enqueue vs
+        // device time), then the same chain replayed from a CUDA graph
+        I.bench_done = true;
+        cudaStream_t st = rt::stream();
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        constexpr int REP = 20;
+        auto run = [&](const char* what, auto&& body) {
+            rt::sync();
+            auto t0 = std::chrono::steady_clock::now();
+            cudaEventRecord(e0, st);
+            for (int i = 0; i < REP; ++i) body();
+            cudaEventRecord(e1, st);
+            auto t1 = std::chrono::steady_clock::now();
+            rt::sync();
+            float ms = 0;
+            cudaEventElapsedTime(&ms, e0, e1);
+            fprintf(stderr, "[lu-bench] %-8s n=%llu levels=%zu: host enqueue %.1f us, device %.1f us per solve\n",
+                    what, (unsigned long long)m_n, I.topo->levels.size(),
+                    std::chrono::duration<double, std::micro>(t1 - t0).count() / REP,
+                    ms * 1e3 / REP);
+        };
+        run("launches", [&] { solve_once(x_dev, b_dev); });
+        run("launches", [&] { solve_once(x_dev, b_dev); });
+        cudaGraph_t g = nullptr;
+        cudaGraphExec_t ge = nullptr;
+        SANM_CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        solve_once(x_dev, b_dev);
+        SANM_CUDA_CHECK(cudaStreamEndCapture(st, &g));
+        SANM_CUDA_CHECK(cudaGraphInstantiate(&ge, g, 0));
+        run("graph", [&] { cudaGraphLaunch(ge, st); });
+        run("graph", [&] { cudaGraphLaunch(ge, st); });
+        cudaGraphExecDestroy(ge);
+        cudaGraphDestroy(g);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    }
+#endif
     if (!I.counters_read) {
         // one 4-byte download per factorisation (the stream is drained here
         // once; the ANM driver synchronises after its first solve anyway)
@@ -1312,10 +1555,14 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
         return;
     }
     char tag[32];
+    static const bool no_hoist = getenv("SANM_LU_NO_HOIST") != nullptr;
     for (auto& L : T.levels) {
         snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - T.levels.data()));
         LuScope ps{tag};
         constexpr int R = FWD_ROWS;
+        // pre-wait prologues (ForwardKernel): not in the first launch of the
+        // sweep, whose predecessor may have produced b
+        const int hoist = no_hoist ? 0 : (&L != T.levels.data());
         if (L.solve_global) {
             constexpr int G = FWD_GROUPS_WIDE;
             rt::for_each_block<256>(
@@ -1327,7 +1574,7 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
                     L.fwd_n, R * G, solve_scratch_doubles<R, G>() * sizeof(double),
                     ForwardKernel<R, G, true>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
                                               T.fwd_tasks.ptr() + L.fwd_off, b_dev,
-                                              T.perm.ptr()});
+                                              T.perm.ptr(), 0});
         } else if (L.max_nc >= SOLVE_WIDE_COLS) {
             constexpr int G = FWD_GROUPS_WIDE;
             rt::for_each_block<R * G>(
@@ -1335,7 +1582,7 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
                     ForwardKernel<R, G>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
                                      T.fwd_tasks.ptr() + L.fwd_off, b_dev,
-                                     T.perm.ptr()});
+                                     T.perm.ptr(), hoist});
         } else {
             constexpr int G = FWD_GROUPS_NARROW;
             rt::for_each_block<R * G>(
@@ -1343,7 +1590,7 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
                     ForwardKernel<R, G>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
                                      T.fwd_tasks.ptr() + L.fwd_off, b_dev,
-                                     T.perm.ptr()});
+                                     T.perm.ptr(), hoist});
         }
     }
     for (size_t l = T.levels.size(); l-- > 0;) {
@@ -1351,6 +1598,8 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
         snprintf(tag, sizeof(tag), "lu_bwd_%02d", (int)l);
         LuScope ps{tag};
         constexpr int R = BWD_ROWS;
+        // not in the first launch: the root's w1' comes from the launch before it
+        const int hoist = no_hoist ? 0 : (l + 1 != T.levels.size());
         if (L.solve_global) {
             constexpr int G = BWD_GROUPS_WIDE;
             rt::for_each_block<256>(
@@ -1361,21 +1610,21 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
             rt::for_each_block<R * G>(
                     L.bwd_n, R * G, solve_scratch_doubles<R, G>() * sizeof(double),
                     BackwardKernel<R, G, true>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
-                                               I.xp.ptr(), x_dev, T.perm.ptr()});
+                                               I.xp.ptr(), x_dev, T.perm.ptr(), 0});
         } else if (L.max_nr >= SOLVE_WIDE_COLS) {
             constexpr int G = BWD_GROUPS_WIDE;
             rt::for_each_block<R * G>(
                     L.bwd_n, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
                     BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
-                                      I.xp.ptr(), x_dev, T.perm.ptr()});
+                                      I.xp.ptr(), x_dev, T.perm.ptr(), hoist});
         } else {
             constexpr int G = BWD_GROUPS_NARROW;
             rt::for_each_block<R * G>(
                     L.bwd_n, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
                     BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
-                                      I.xp.ptr(), x_dev, T.perm.ptr()});
+                                      I.xp.ptr(), x_dev, T.perm.ptr(), hoist});
         }
     }
 }

@@ -1069,6 +1069,23 @@ Symbolic symbolic_analyze(uint32_t n, const uint32_t* rowptr,
         for (u32 s = 0; s < nsn; ++s) S.level_list[pos[lev[s]]++] = s;
     }
 
+    if (getenv("SANM_LU_DEBUG")) {
+        for (u32 l = 0; l + 1 < S.level_ptr.size(); ++l) {
+            u32 mx_nr = 0, mx_nc = 0, nchain = 0;
+            u64 ent = 0;
+            for (u32 q = S.level_ptr[l]; q < S.level_ptr[l + 1]; ++q) {
+                const u32 s = S.level_list[q];
+                mx_nr = std::max(mx_nr, S.sn_nr[s]);
+                mx_nc = std::max(mx_nc, S.sn_nc[s]);
+                ent += (u64)S.sn_nc[s] * (2 * S.sn_nr[s] - S.sn_nc[s]);
+                if (S.child_ptr[s + 1] - S.child_ptr[s] == 1) ++nchain;
+            }
+            fprintf(stderr, "[sanm_lu] level %2u: %5u fronts (%u with one child), max nr %5u, max nc %5u, %9llu entries\n",
+                    l, S.level_ptr[l + 1] - S.level_ptr[l], nchain, mx_nr, mx_nc,
+                    (unsigned long long)ent);
+        }
+    }
+
     SANM_STAGE("destinations of the original entries");
     // ---- destinations of the original entries
     S.a_dest.resize(rowptr[n]);
