@@ -533,6 +533,9 @@ def fea_binary_solves(with_cpu: bool, mt_threads: int):
         shutil.rmtree(d, ignore_errors=True)
         return row
 
+    # largest sys-mtN.json of the reference's config directory that the host
+    # can run (N = min(32, cores))
+    mt = max([n for n in (1, 2, 4, 8, 16, 32) if n <= mt_threads] or [1])
     rows = []
     for name, cfgs in FEA_CASES:
         row = {"config": name, "gpu_fea": one(fea_diff.GPU_FEA, cfgs)}
@@ -541,6 +544,16 @@ def fea_binary_solves(with_cpu: bool, mt_threads: int):
         for row, (name, cfgs) in zip(rows, FEA_CASES):
             row["ref_fea"] = one(fea_diff.REF_FEA, cfgs)
             row["ref_fea"]["threads"] = 1
+            if mt > 1:
+                # the same application at sys-mtN.json, the shared
+                # constant pools pre-sized (oracle/shim/presize_pool.cpp)
+                os.environ["SANM_REF_PRESIZE_ELEMS"] = "8000000"
+                try:
+                    row["ref_fea_mt"] = one(fea_diff.REF_FEA, cfgs,
+                                            "sys-mt%d.json" % mt)
+                finally:
+                    del os.environ["SANM_REF_PRESIZE_ELEMS"]
+                row["ref_fea_mt"]["threads"] = mt
             row["iters_match"] = (row["gpu_fea"]["anm_iters"] ==
                                   row["ref_fea"]["anm_iters"])
             g, r = row["gpu_fea"], row["ref_fea"]
