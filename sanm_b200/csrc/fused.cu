@@ -222,13 +222,13 @@ struct StepKernel {
             const int j = kb - i;
             ld_strided<S>(Si, slot_ptr<M>(a, t, i));
             ld_strided<S>(Sj, slot_ptr<M>(a, t, j));
-            M::accum(acc, Si, Sj, i, j);
-            M::accum(acc, Sj, Si, j, i);
+            M::accum(acc, Si, Sj, i, j, a.pr);
+            M::accum(acc, Sj, Si, j, i, a.pr);
         }
         if (kb % 2 == 0) {
             const int i = kb / 2;
             ld_strided<S>(Si, slot_ptr<M>(a, t, i));
-            M::accum(acc, Si, Si, i, i);
+            M::accum(acc, Si, Si, i, i, a.pr);
         }
     }
 
@@ -383,9 +383,19 @@ void FusedProp::launch_step(int k_push, int kb, bool want_out, const double* x) 
         // register file allows; __launch_bounds__(128, 1) (255 registers) gives
         // 1.76 G tet*order/s where (128, 5) gives 2.49 G
         if (use_io) {
-            rt::for_each_block<TILE, M::MINB>(
-                    ntiles, TILE, smem,
-                    StepKernel<M, true>{a, io, k_push, kb, (int)want_out});
+            // SANM_STEP_MINB = 4 | 5 | 6 overrides the occupancy target (tuning
+            // knob, tools/step_variants.sh)
+            static const int minb = getenv("SANM_STEP_MINB") ? atoi(getenv("SANM_STEP_MINB")) : M::MINB;
+            StepKernel<M, true> k{a, io, k_push, kb, (int)want_out};
+            if (minb == M::MINB) {
+                rt::for_each_block<TILE, M::MINB>(ntiles, TILE, smem, k);
+            } else if (minb == 4) {
+                rt::for_each_block<TILE, 4>(ntiles, TILE, smem, k);
+            } else if (minb == 5) {
+                rt::for_each_block<TILE, 5>(ntiles, TILE, smem, k);
+            } else {
+                rt::for_each_block<TILE, 6>(ntiles, TILE, smem, k);
+            }
         } else {
             rt::for_each_block(
                     ntiles, TILE, smem,

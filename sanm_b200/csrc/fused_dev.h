@@ -158,7 +158,7 @@ struct NHC {
     }
     //! contribution of the ordered pair (i, j), i + j = kb
     SANM_HD static void accum(Acc& a, const double* Si, const double* Sj,
-                              int /*i*/, int j) {
+                              int /*i*/, int j, const Params& /*pr*/) {
         const double* Gi = Si + oG;
         const double* Fj = Sj + oF;
         mm3_acc(a.G, Gi, Fj, -1.0);
@@ -216,12 +216,16 @@ struct NHI {
     static constexpr int MINB = 4;
     static constexpr int AUX = 0;
     enum { oF = 0, oG = 9, oL = 18, oJ = 19, oQ = 20, oI = 21, oT = 22 };
+    //! P = c0 sum Q_i F_j + c1 sum T_j G_i^T: the two products only ever
+    //! enter the stress bias in this combination, so they share one
+    //! accumulator (24 doubles of accumulators instead of 33: registers that
+    //! hold loads in flight instead)
     struct Acc {
-        double G[9], QF[9], TG[9], L, J, Q, Ic, A, JJ;
+        double G[9], P[9], L, J, Q, Ic, A, JJ;
     };
     SANM_HD static void zero(Acc& a) {
 #pragma unroll
-        for (int q = 0; q < 9; ++q) a.G[q] = a.QF[q] = a.TG[q] = 0;
+        for (int q = 0; q < 9; ++q) a.G[q] = a.P[q] = 0;
         a.L = a.J = a.Q = a.Ic = a.A = a.JJ = 0;
     }
     SANM_HD static void eval0(const double* F0, double* s0, double* /*aux*/,
@@ -251,7 +255,7 @@ struct NHI {
                                 pr.c[1] * T0 * G0[c * 3 + r];
     }
     SANM_HD static void accum(Acc& a, const double* Si, const double* Sj,
-                              int /*i*/, int j) {
+                              int /*i*/, int j, const Params& pr) {
         const double* Gi = Si + oG;
         const double* Fi = Si + oF;
         const double* Fj = Sj + oF;
@@ -265,12 +269,12 @@ struct NHI {
         a.Ic += dot9(Fi, Fj);
         a.A += Qi * Ij;
         a.JJ += Ji * Jj;
-#pragma unroll
-        for (int q = 0; q < 9; ++q) a.QF[q] += Qi * Fj[q];
+        const double cq = pr.c[0] * Qi, ct = pr.c[1] * Tj;
 #pragma unroll
         for (int r = 0; r < 3; ++r)
 #pragma unroll
-            for (int c = 0; c < 3; ++c) a.TG[r * 3 + c] += Tj * Gi[c * 3 + r];
+            for (int c = 0; c < 3; ++c)
+                a.P[r * 3 + c] += cq * Fj[r * 3 + c] + ct * Gi[c * 3 + r];
     }
     SANM_HD static void scalars(double L, double sJ, double sQ, double Ic,
                                 double sA, double sJJ, const double* s0,
@@ -301,9 +305,9 @@ struct NHI {
 #pragma unroll
             for (int c = 0; c < 3; ++c)
                 Pb[r * 3 + c] =
-                        pr.c[0] * (Qb * F0[r * 3 + c] + a.QF[r * 3 + c]) +
-                        pr.c[1] * (T0 * Gb[c * 3 + r] + Tb * G0[c * 3 + r] +
-                                   a.TG[r * 3 + c]);
+                        pr.c[0] * Qb * F0[r * 3 + c] +
+                        pr.c[1] * (T0 * Gb[c * 3 + r] + Tb * G0[c * 3 + r]) +
+                        a.P[r * 3 + c];
     }
     SANM_HD static void tangent(const double* Fk, const double* s0,
                                 const double* /*aux*/, const Params& pr,
@@ -362,7 +366,7 @@ struct ARAP {
         for (int q = 0; q < 9; ++q) P0[q] = pr.c[0] * F0[q] + pr.c[1] * W[q];
     }
     SANM_HD static void accum(Acc& a, const double* Si, const double* Sj,
-                              int /*i*/, int /*j*/) {
+                              int /*i*/, int /*j*/, const Params& /*pr*/) {
         const double *Mi = Si + oF, *Pi = Si + oP;
         const double *Mj = Sj + oF, *Pj = Sj + oP, *Wj = Sj + oW;
 #pragma unroll
