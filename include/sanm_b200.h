@@ -162,6 +162,17 @@ int sanm_remap_identity(int in_rank, const uint64_t* in_dims, int out_rank,
 int sanm_remap_destroy(sanm_remap_t* r);
 /* SparseLinearDesc::apply, anm.h:62 */
 int sanm_remap_apply(sanm_remap_t* r, const double* x, double* y);
+/* No counterpart in the reference: added
+ * for callers that cannot allocate device memory (CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  Same
+ * result as sanm_remap_apply (x, y host vectors), but the device staging
+ * lives in a static device array of SANM_REMAP_STATIC_MAX_DOUBLES doubles
+ * (16 MiB, held by every GPU that loads the library): the call performs no
+ * cudaMalloc / cudaFree / pool allocation.  Fails with SANM_ERR_ASSERT when
+ * round_up(nr_in, 32) + nr_out exceeds the limit.  All calls share the array:
+ * calls that overlap on one GPU race -- one call at a time per device. */
+#define SANM_REMAP_STATIC_MAX_DOUBLES 2097152
+int sanm_remap_apply_static(sanm_remap_t* r, const double* x, double* y);
 
 /* ---- fused element phase of one series expansion ---------------------------
  * The element side of ANMDriverHelper::solve_expansion_coeffs

@@ -392,6 +392,15 @@ class SparseLinearDesc:
         self.b.call("remap_apply", self.h, _ptr(x), _ptr(y))
         return y
 
+    def apply_static(self, x) -> np.ndarray:
+        """sanm_remap_apply_static: the same gather staged in the library's
+        static device scratch (no device allocation)"""
+        x = _f64(x)
+        assert x.size == int(np.prod(self.inp_shape))
+        y = np.empty(self.out_shape)
+        self.b.call("remap_apply_static", self.h, _ptr(x), _ptr(y))
+        return y
+
 
 class SparseSolver:
     """libsanm/sparse_solver.h:17-87"""

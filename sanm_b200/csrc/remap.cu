@@ -1,6 +1,10 @@
 /* sanm_b200/csrc/remap.cu -- see remap.h. */
 #include "remap.h"
 
+#include <mutex>
+
+#include "capi_util.h"
+
 namespace sanm_b200 {
 
 namespace {
@@ -80,4 +84,75 @@ void Remap::apply(double* y, VecLayout ylay, const double* x,
                                        nr_out(), ylay.e});
 }
 
+/* ---- allocation-free apply (sanm_remap_apply_static) -----------------------
+ * sanm_remap_apply stages the caller's host vectors in two device buffers that
+ * it takes from the stream-ordered pool on every call.  Callers that must not
+ * allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc) get the same gather with that scratch in a file-scope
+ * device array instead: SANM_REMAP_STATIC_MAX_DOUBLES doubles (16 MiB), held by
+ * every GPU that loads the library until exit.  Layout: x at offset 0, y at the
+ * next 256-byte boundary after x.
+ *
+ * g_apply_scratch is a DEVICE symbol: in host code its name is only a host-side
+ * stand-in, never a device address.  The address the kernel gets comes from
+ * cudaGetSymbolAddress, asked once per device with that device current.
+ * All calls share the array and it keeps the last call's contents; the y part
+ * is cleared before every apply.  Calls that overlap on the GPU (several
+ * streams or host threads) race on it: one call at a time per device. */
+namespace {
+constexpr uint64_t STATIC_DOUBLES = SANM_REMAP_STATIC_MAX_DOUBLES;
+#ifdef SANM_HOSTEMU
+alignas(256) double g_apply_scratch[STATIC_DOUBLES];
+double* apply_scratch() { return g_apply_scratch; }
+#else
+static __device__ __align__(256) double g_apply_scratch[STATIC_DOUBLES];
+
+double* apply_scratch() {
+    rt::check_device();
+    constexpr int MAX_DEV = 64;
+    static double* ptr[MAX_DEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    SANM_CUDA_CHECK(cudaGetDevice(&dev));
+    sanm_check(dev >= 0 && dev < MAX_DEV, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk{mu};
+    if (!ptr[dev]) {
+        double* p = nullptr;
+        SANM_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_apply_scratch));
+        sanm_check(p != nullptr, "cudaGetSymbolAddress returned a null address");
+        ptr[dev] = p;
+    }
+    return ptr[dev];
+}
+#endif
+}  // namespace
+
+void Remap::apply_static(double* y_host, const double* x_host) const {
+    const uint64_t nin = nr_in(), nout = nr_out();
+    const uint64_t yoff = (nin + 31) / 32 * 32;  // 256-byte boundary
+    if (yoff + nout > STATIC_DOUBLES) {
+        sanm_throw(SANM_ERR_ASSERT,
+                   "sanm_remap_apply_static: %zu input + %zu output doubles exceed "
+                   "the static scratch of %zu doubles "
+                   "(SANM_REMAP_STATIC_MAX_DOUBLES); use sanm_remap_apply",
+                   (size_t)nin, (size_t)nout, (size_t)STATIC_DOUBLES);
+    }
+    double* sx = apply_scratch();
+    double* sy = sx + yoff;
+    // the array keeps the previous call's contents: rows without entries and
+    // every other output start from zero
+    rt::dzero(sy, nout * sizeof(double));
+    rt::h2d(sx, x_host, nin * sizeof(double));
+    apply(sy, VecLayout{}, sx, VecLayout{});
+    rt::d2h(y_host, sy, nout * sizeof(double));
+}
+
 }  // namespace sanm_b200
+
+extern "C" int sanm_remap_apply_static(sanm_remap_t* r, const double* x, double* y) {
+    using namespace sanm_b200;
+    return capi::guard([&] {
+        sanm_check(r && x && y);
+        r->r->apply_static(y, x);
+    });
+}

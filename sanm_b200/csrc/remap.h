@@ -36,6 +36,10 @@ public:
     //! y = A x on the device; x, y are device pointers with the given layouts
     void apply(double* y, VecLayout ylay, const double* x, VecLayout xlay) const;
 
+    //! y = A x for host vectors, staged in the library's static device scratch
+    //! (no allocation; remap.cu, sanm_remap_apply_static)
+    void apply_static(double* y_host, const double* x_host) const;
+
     //! host views (kept for K's symbolic analysis)
     const std::vector<uint32_t>& h_rowptr() const { return m_h_rowptr; }
     const std::vector<uint32_t>& h_idx() const { return m_h_idx; }
