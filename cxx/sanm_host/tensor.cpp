@@ -2,6 +2,7 @@
 // (interface: libsanm/tensor.h:17-604; semantics checked against
 // libsanm/tensor.cpp, tensor_elemwise.cpp, tensor_linalg.cpp).  Plain loops:
 // nothing here is on the propagation path, which runs in libsanm_b200.so.
+#include <sys/mman.h>
 #include "sanm_host/tensor.hpp"
 
 #include "sanm_b200.h"
@@ -202,7 +203,9 @@ TensorShape infer_reduce_shape(const TensorShape& src, int axis,
 
 // ------------------------------------------------------------ TensorStorage
 TensorStorage::~TensorStorage() {
-    std::free(m_data);
+    if (m_kind == Kind::PLAIN)
+        std::free(m_data);
+    // pool storages live until exit (their address range is never returned)
 }
 
 void TensorStorage::ensure_size(size_t size) {
@@ -219,25 +222,51 @@ void TensorStorage::ensure_size(size_t size) {
     m_cap = want;
 }
 
+/* The shared zero / one pools (libsanm/tensor.cpp:251-293).  As in the
+ * reference there is ONE storage object per constant, so every all-zero tensor
+ * has the same storage and the same pointer, whatever its size
+ * (tests/tensor.cpp "Tensor.Constant").  The reference grows that storage by
+ * reallocating it, which moves memory under concurrent readers (SURVEY section
+ * 0).  Here each pool is a reserved address range (64 GiB of virtual memory,
+ * committed page by page as it is touched) that never moves: growth only
+ * extends the initialised prefix, under a mutex, and readers of a shorter
+ * prefix are unaffected.  Anonymous pages read as zero, so the zero pool costs
+ * nothing until someone reads it. */
 template <TensorStorage::Constant val>
 const std::shared_ptr<const TensorStorage>& TensorStorage::constant(
         size_t size) {
-    // pool: the newest (largest) block; older blocks stay alive for as long as
-    // a tensor references them, so readers never see memory move
+    static size_t RESERVE = size_t(1) << 33;  // elements
     static std::mutex mtx;
-    static std::shared_ptr<const TensorStorage> pool =
-            std::make_shared<TensorStorage>();
-    static thread_local std::shared_ptr<const TensorStorage> local;
-    std::lock_guard<std::mutex> lk{mtx};
-    if (size > pool->size() || pool->kind() == Kind::PLAIN) {
+    static const std::shared_ptr<TensorStorage> pool = [] {
         auto blk = std::make_shared<TensorStorage>();
-        blk->ensure_size(std::max<size_t>(size, 1));
+        void* p = MAP_FAILED;
+        // strict-overcommit hosts may refuse the large range: halve until taken
+        for (; RESERVE >= (size_t(1) << 24); RESERVE >>= 1) {
+            p = mmap(nullptr, RESERVE * sizeof(fp_t), PROT_READ | PROT_WRITE,
+                     MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+            if (p != MAP_FAILED)
+                break;
+        }
+        if (p == MAP_FAILED)
+            throw SANMError{"can not reserve the address range of a constant pool"};
+        blk->m_data = static_cast<fp_t*>(p);
+        blk->m_cap = 0;
         blk->m_kind = val == Constant::ZERO ? Kind::ZERO : Kind::ONE;
-        std::fill_n(blk->m_data, blk->m_cap, val == Constant::ZERO ? 0. : 1.);
-        pool = std::move(blk);
+        return blk;
+    }();
+    static const std::shared_ptr<const TensorStorage> cpool = pool;
+    if (size > pool->m_cap) {
+        std::lock_guard<std::mutex> lk{mtx};
+        if (size > pool->m_cap) {
+            sanm_assert(size <= RESERVE, "constant tensor of %zu elements", size);
+            size_t want = std::max(size, pool->m_cap * 2);
+            want = std::min(want, RESERVE);
+            if (val == Constant::ONE)
+                std::fill(pool->m_data + pool->m_cap, pool->m_data + want, 1.);
+            pool->m_cap = want;
+        }
     }
-    local = pool;
-    return local;
+    return cpool;
 }
 template const std::shared_ptr<const TensorStorage>&
         TensorStorage::constant<TensorStorage::Constant::ZERO>(size_t);
@@ -585,7 +614,14 @@ void binary(TensorND& dst, const TensorND& lhs, const TensorND& rhs,
         }
     }
 
-    TensorND l = lhs, r = rhs;  // keep the sources alive across detach
+    // keep the sources alive across detach -- but not the aliased one: a
+    // second reference to dst's own buffer would force rwptr() to copy it, and
+    // `a -= b` must keep a's storage (tests/tensor.cpp "Tensor.SimpleArith")
+    TensorND l, r;
+    if (&dst != &lhs)
+        l = lhs;
+    if (&dst != &rhs)
+        r = rhs;
     fp_t* d;
     if (alias || accum) {
         d = dst.rwptr();
@@ -1215,10 +1251,34 @@ const TensorND& TensorND::compute_batched_svd_w(TensorND& u, TensorND& s,
         auto make_w = [&]() { gemm(W, U, Vs.data(), n, n, n, false, true, false); };
         make_w();
         if (require_rotation && det_general(W, n, tmp, piv) < 0) {
-            size_t j = n - 1;  // smallest singular value
-            ps[b * n + j] = -ps[b * n + j];
-            for (size_t i = 0; i < n; ++i)
-                Vs[i * n + j] = -Vs[i * n + j];
+            // negate singular values (and their U columns) so that det W = 1,
+            // chosen as libsanm/tensor_svd.cpp:93-121 chooses them: the first
+            // group of (nearly) equal values with the fewest members -- a
+            // single value, or all of an odd-sized group
+            constexpr fp_t EPS = 1e-3;
+            fp_t* S = ps + b * n;
+            int best_idx = -1, best_nr = int(n) + 1;
+            for (size_t i = 0; i < n; ++i) {
+                size_t j = i + 1;
+                while (j < n && std::fabs(S[i] - S[j]) < EPS)
+                    ++j;
+                int nr = int(j - i);
+                if (nr <= best_nr || (nr == best_nr + 1 && nr % 2 == 1)) {
+                    best_idx = int(i);
+                    best_nr = nr;
+                    if (nr == 1)
+                        break;
+                }
+                i = j;  // and the loop increments once more, as the reference's does
+            }
+            int lo = best_idx, hi = best_idx + 1;
+            if (!(best_nr == 1 || best_nr % 2 == 0))
+                hi = best_idx + best_nr;
+            for (int j = lo; j < hi; ++j) {
+                S[j] = -S[j];
+                for (size_t i = 0; i < n; ++i)
+                    U[i * n + j] = -U[i * n + j];
+            }
             make_w();
         }
     }

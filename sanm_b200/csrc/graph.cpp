@@ -352,8 +352,9 @@ Lowered lower_graph(const Graph& g, int out_var, const Shape& x_shape) {
                 const Shape& s = in_shape(0);
                 sanm_check(s.rank == 3 && s.dim[1] == s.dim[2],
                            "invalid shape for SVD-W: %s", s.str().c_str());
-                sanm_check(s.dim[1] == 3,
-                           "SVD-W is implemented for 3x3 matrices only");
+                sanm_check(s.dim[1] >= 2 && s.dim[1] <= (uint64_t)MAXD,
+                           "SVD-W is implemented for 2x2 .. %dx%d matrices", MAXD,
+                           MAXD);
                 L.vars[lo.out[0]].shape = s;
                 L.vars[lo.out[1]].shape = Shape{s.dim[0], s.dim[1]};
                 L.vars[lo.out[2]].shape = s;
@@ -490,12 +491,13 @@ Lowered lower_graph(const Graph& g, int out_var, const Shape& x_shape) {
                 break;
             case OP_SVDW:
                 elemwise = false;
-                lo.eaux0 = 12;
+                // [U0, S0]; self-bias [D, Bpw]; hidden stack P_k (n x n items)
+                lo.eaux0 = eo(0) + eo(1);
                 if (nc(0)) {
                     L.vars[lo.in[0]].needs_stack = true;
                     L.vars[lo.out[2]].needs_stack = true;
-                    lo.esb = 18;
-                    lo.eauxk = 9;
+                    lo.esb = 2 * eo(0);
+                    lo.eauxk = eo(0);
                 }
                 break;
             default:
@@ -516,6 +518,9 @@ Lowered lower_graph(const Graph& g, int out_var, const Shape& x_shape) {
     for (auto& lo : L.ops) {
         if (lo.type == OP_SVDW && !lo.const_op &&
             (readers[lo.out[0]] || readers[lo.out[1]])) {
+            sanm_check(L.vars[lo.out[0]].e == 9,
+                       "full-mode SVD-W (U or S read) is implemented for 3x3 "
+                       "matrices only; the polar mode (W only) for any size");
             lo.svdw_full = true;
             for (int q = 0; q < 3; ++q) L.vars[lo.out[q]].needs_stack = true;
             lo.esb = 27;    // Bu, Bw, Mbias

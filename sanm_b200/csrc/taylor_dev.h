@@ -41,7 +41,11 @@ namespace taylor {
 
 constexpr int MAX_IN = 8;      //!< max inputs of one op (LinearCombination / Concat)
 constexpr int MAXD = 7;        //!< max matrix dim handled by the generic paths
-constexpr int MAXE = MAXD * MAXD;
+//! max elements per item of any variable (matrices up to MAXD x MAXD; plain
+//! element-wise / reduction operands up to 64: the reference's
+//! tests/symbolic.cpp reduces 9 x 7 items)
+constexpr int MAXE = 64;
+static_assert(MAXE >= MAXD * MAXD, "MAXE");
 constexpr int MAX_ORDER = 48;  //!< bound for per-thread polynomial scratch
 
 enum OpType : int {
@@ -595,6 +599,214 @@ SANM_HD inline void svdw3_fwd_p(double* Pk, double* Wk, const double* Mk,
     for (int r = 0; r < 3; ++r)
 #pragma unroll
         for (int c = 0; c < 3; ++c) Wk[r * 3 + c] = WkT[c * 3 + r];
+}
+
+/* ---------------- general n (2 .. MAXD): runtime-size versions of the above.
+ * The reference runs SVD-W on any square size (libsanm/tensor_svd.cpp:48-145,
+ * Eigen::Dynamic path; tests/symbolic.cpp:658-716 use 4x4); `fea` only ever
+ * uses 3x3, which keeps the unrolled code above.  Row-major n x n arrays. */
+constexpr int MAXM = MAXD * MAXD;  //!< elements of the largest matrix
+
+//! C = op(A) op(B), n x n, ta / tb = transpose flags
+SANM_HD inline void mmn(double* C, const double* A, const double* B, int n,
+                        bool ta, bool tb) {
+    for (int r = 0; r < n; ++r) {
+        for (int c = 0; c < n; ++c) {
+            double s = 0;
+            for (int q = 0; q < n; ++q) {
+                s += (ta ? A[q * n + r] : A[r * n + q]) *
+                     (tb ? B[c * n + q] : B[q * n + c]);
+            }
+            C[r * n + c] = s;
+        }
+    }
+}
+
+//! sign of det(A) by elimination with partial pivoting (A orthogonal here)
+SANM_HD inline double det_sign_n(const double* A, int n) {
+    double T[MAXM];
+    for (int i = 0; i < n * n; ++i) T[i] = A[i];
+    double sg = 1;
+    for (int k = 0; k < n; ++k) {
+        int piv = k;
+        for (int i = k + 1; i < n; ++i) {
+            if (fabs(T[i * n + k]) > fabs(T[piv * n + k])) piv = i;
+        }
+        if (T[piv * n + k] == 0) return 0;
+        if (piv != k) {
+            sg = -sg;
+            for (int c = 0; c < n; ++c) {
+                double x = T[k * n + c];
+                T[k * n + c] = T[piv * n + c];
+                T[piv * n + c] = x;
+            }
+        }
+        if (T[k * n + k] < 0) sg = -sg;
+        for (int i = k + 1; i < n; ++i) {
+            double f = T[i * n + k] / T[k * n + k];
+            for (int c = k + 1; c < n; ++c) T[i * n + c] -= f * T[k * n + c];
+        }
+    }
+    return sg;
+}
+
+//! svd3 for n x n: one-sided Jacobi, s sorted decreasing
+SANM_HD inline void svdn(const double* M, int n, double* L, double* s, double* R) {
+    double A[MAXM], V[MAXM], nrm[MAXD];
+    int idx[MAXD], good[MAXD];
+    for (int i = 0; i < n * n; ++i) {
+        A[i] = M[i];
+        V[i] = (i % (n + 1) == 0) ? 1.0 : 0.0;
+    }
+    for (int sweep = 0; sweep < 40; ++sweep) {
+        double off = 0;
+        for (int p = 0; p < n - 1; ++p) {
+            for (int q = p + 1; q < n; ++q) {
+                double app = 0, aqq = 0, apq = 0;
+                for (int r = 0; r < n; ++r) {
+                    app += A[r * n + p] * A[r * n + p];
+                    aqq += A[r * n + q] * A[r * n + q];
+                    apq += A[r * n + p] * A[r * n + q];
+                }
+                double lim = 1e-32 * app * aqq;
+                if (apq * apq <= lim || apq == 0) continue;
+                off += fabs(apq);
+                double zeta = (aqq - app) / (2 * apq);
+                double tt = (zeta >= 0 ? 1.0 : -1.0) /
+                            (fabs(zeta) + sqrt(1 + zeta * zeta));
+                double cs = 1.0 / sqrt(1 + tt * tt), sn = cs * tt;
+                for (int r = 0; r < n; ++r) {
+                    double x = A[r * n + p], y = A[r * n + q];
+                    A[r * n + p] = cs * x - sn * y;
+                    A[r * n + q] = sn * x + cs * y;
+                    x = V[r * n + p];
+                    y = V[r * n + q];
+                    V[r * n + p] = cs * x - sn * y;
+                    V[r * n + q] = sn * x + cs * y;
+                }
+            }
+        }
+        if (off == 0) break;
+    }
+    for (int c = 0; c < n; ++c) {
+        double q = 0;
+        for (int r = 0; r < n; ++r) q += A[r * n + c] * A[r * n + c];
+        nrm[c] = sqrt(q);
+        idx[c] = c;
+    }
+    for (int i = 0; i < n - 1; ++i) {
+        for (int j = 0; j < n - 1 - i; ++j) {
+            if (nrm[idx[j]] < nrm[idx[j + 1]]) {
+                int tmp = idx[j];
+                idx[j] = idx[j + 1];
+                idx[j + 1] = tmp;
+            }
+        }
+    }
+    for (int c = 0; c < n; ++c) {
+        s[c] = nrm[idx[c]];
+        for (int r = 0; r < n; ++r) R[r * n + c] = V[r * n + idx[c]];
+    }
+    const double smax = s[0] > 0 ? s[0] : 1.0;
+    for (int c = 0; c < n; ++c) {
+        good[c] = s[c] > 1e-300 && s[c] > 1e-14 * smax;
+        if (good[c]) {
+            double inv = 1.0 / s[c];
+            for (int r = 0; r < n; ++r) L[r * n + c] = A[r * n + idx[c]] * inv;
+        }
+    }
+    // rank-deficient columns: complete L to an orthogonal matrix (the unit
+    // vector with the largest remainder after projecting out the columns
+    // already there; the singular values are sorted, so those come first)
+    for (int c = 0; c < n; ++c) {
+        if (good[c]) continue;
+        double best = -1, v[MAXD], bv[MAXD];
+        for (int j = 0; j < n; ++j) {
+            for (int r = 0; r < n; ++r) v[r] = r == j ? 1.0 : 0.0;
+            for (int pass = 0; pass < 2; ++pass) {
+                for (int q = 0; q < c; ++q) {
+                    double d = 0;
+                    for (int r = 0; r < n; ++r) d += L[r * n + q] * v[r];
+                    for (int r = 0; r < n; ++r) v[r] -= d * L[r * n + q];
+                }
+            }
+            double q2 = 0;
+            for (int r = 0; r < n; ++r) q2 += v[r] * v[r];
+            if (q2 > best) {
+                best = q2;
+                for (int r = 0; r < n; ++r) bv[r] = v[r];
+            }
+        }
+        double inv = 1.0 / sqrt(best);
+        for (int r = 0; r < n; ++r) L[r * n + c] = bv[r] * inv;
+    }
+}
+
+//! svdw3 for n x n (libsanm/tensor_svd.cpp:48-145)
+SANM_HD inline void svdwn(const double* M, int n, bool require_rotation,
+                          double* U, double* S, double* W) {
+    double R[MAXM];
+    svdn(M, n, U, S, R);
+    if (require_rotation && ((det_sign_n(U, n) < 0) != (det_sign_n(R, n) < 0))) {
+        const double EPS = 1e-3;
+        int best_idx = -1, best_nr = n + 1;
+        for (int i = 0; i < n; ++i) {
+            int j = i + 1;
+            while (j < n && fabs(S[i] - S[j]) < EPS) ++j;
+            int nr = j - i;
+            if (nr <= best_nr || (nr == best_nr + 1 && nr % 2 == 1)) {
+                best_idx = i;
+                best_nr = nr;
+                if (nr == 1) break;
+            }
+            i = j;  // the reference's loop also does ++i afterwards
+        }
+        int lo = best_idx, hi = best_idx + 1;
+        if (!(best_nr == 1 || best_nr % 2 == 0)) hi = best_idx + best_nr;
+        for (int c = lo; c < hi; ++c) {
+            S[c] = -S[c];
+            for (int r = 0; r < n; ++r) U[r * n + c] = -U[r * n + c];
+        }
+    }
+    mmn(W, U, R, n, false, true);  // W = U R^T
+}
+
+//! svdw3_fwd_p for n x n (libsanm/tensor_svd.cpp:389-475), same formulas
+SANM_HD inline void svdwn_fwd_p(double* Pk, double* Wk, const double* Mk,
+                                const double* U, const double* S,
+                                const double* W, const double* D,
+                                const double* Bpw, int n) {
+    double t0[MAXM], t1[MAXM], G[MAXM], x[MAXM];
+    mmn(t0, U, D, n, true, false);   // U^T D
+    mmn(t1, t0, U, n, false, false); // U^T D U; E = its transpose
+    mmn(t0, U, W, n, true, false);   // U^T W
+    mmn(x, t0, Mk, n, false, true);  // (U^T W) Mk^T
+    mmn(G, x, U, n, false, false);
+    for (int r = 0; r < n; ++r)
+        for (int c = 0; c < n; ++c) G[r * n + c] *= S[r];
+    for (int r = 0; r < n; ++r)
+        for (int c = 0; c < n; ++c)
+            x[r * n + c] = clip_div(t1[c * n + r] + G[r * n + c] + G[c * n + r],
+                                    S[r] + S[c]);
+    // PkT = U x U^T
+    mmn(t0, U, x, n, false, false);
+    mmn(t1, t0, U, n, false, true);  // t1 = PkT
+    for (int r = 0; r < n; ++r)
+        for (int c = 0; c < n; ++c) Pk[r * n + c] = t1[c * n + r];
+    // Q = Mk^T - Bpw^T - W^T PkT
+    mmn(t0, W, t1, n, true, false);
+    for (int r = 0; r < n; ++r)
+        for (int c = 0; c < n; ++c)
+            G[r * n + c] = Mk[c * n + r] - Bpw[c * n + r] - t0[r * n + c];
+    // WkT = Q U S^-1 U^T
+    mmn(t0, G, U, n, false, false);
+    for (int c = 0; c < n; ++c) {
+        const double si = clip_div(1.0, S[c]);
+        for (int r = 0; r < n; ++r) t0[r * n + c] *= si;
+    }
+    mmn(t1, t0, U, n, false, true);
+    for (int r = 0; r < n; ++r)
+        for (int c = 0; c < n; ++c) Wk[r * n + c] = t1[c * n + r];
 }
 
 /*!
@@ -1313,6 +1525,71 @@ SANM_HD inline void op_svdw_full(const DOp& op, const ItemCtx& c) {
     }
 }
 
+//! polar mode of SVD-W for n x n items, n != 3 (see op_svdw for the caches:
+//! aux0 = [U0 (n^2), S0 (n)], self-bias = [D, Bpw] (2 n^2), hidden stack P_k)
+SANM_HD inline void op_svdw_n(const DOp& op, const ItemCtx& c, int n) {
+    const DVar &xv = c.var(op.in[0]), &wv = c.var(op.out[2]);
+    const int64_t np = c.np;
+    const size_t t = c.t;
+    const int e = n * n;
+    double U[MAXM], S[MAXD], W[MAXM];
+    if (c.phase == PH_EVAL) {
+        double M[MAXM];
+        ld_mat<0>(M, xv, 0, np, t, e);
+        svdwn(M, n, op.i[0] != 0, U, S, W);
+        st_buf<0>(op.aux0, U, np, t, e);
+        st_buf<0>(op.aux0 + (int64_t)e * np, S, np, t, n);
+        st_buf<0>(wv.p0, W, np, t, e);
+        st_buf<0>(c.var(op.out[0]).p0, U, np, t, e);
+        st_buf<0>(c.var(op.out[1]).p0, S, np, t, n);
+        return;
+    }
+    const int k = c.k;
+    double D[MAXM], Bpw[MAXM];
+    zero_arr<0>(D, e);
+    zero_arr<0>(Bpw, e);
+    if (c.phase == PH_BIAS) {
+        double A[MAXM], B[MAXM];
+        for (int i = 1; i < k; ++i) {
+            // Bm += M_i M_{k-i}^T
+            ld_mat<0>(A, xv, i, np, t, e);
+            ld_mat<0>(B, xv, k - i, np, t, e);
+            for (int r = 0; r < n; ++r)
+                for (int cc = 0; cc < n; ++cc) {
+                    double q = 0;
+                    for (int m = 0; m < n; ++m) q += A[r * n + m] * B[cc * n + m];
+                    D[r * n + cc] += q;
+                }
+            // Bp += P_i^T P_{k-i} ;  Bpw += P_i W_{k-i}
+            ld_buf<0>(A, op.auxk + (int64_t)i * op.auxk_stride, np, t, e);
+            ld_buf<0>(B, op.auxk + (int64_t)(k - i) * op.auxk_stride, np, t, e);
+            for (int r = 0; r < n; ++r)
+                for (int cc = 0; cc < n; ++cc) {
+                    double q = 0;
+                    for (int m = 0; m < n; ++m) q += A[m * n + r] * B[m * n + cc];
+                    D[r * n + cc] -= q;
+                }
+            ld_mat<0>(B, wv, k - i, np, t, e);
+            mm_acc<0, 0, 0>(Bpw, A, B, n, n, n);
+        }
+        st_buf<0>(op.sb, D, np, t, e);
+        st_buf<0>(op.sb + (int64_t)e * np, Bpw, np, t, e);
+    } else if (!c.sb_zero) {
+        ld_buf<0>(D, op.sb, np, t, e);
+        ld_buf<0>(Bpw, op.sb + (int64_t)e * np, np, t, e);
+    }
+    double Mk[MAXM], Pk[MAXM], Wk[MAXM];
+    ld_mat<0>(Mk, xv, k, np, t, e);
+    ld_buf<0>(U, op.aux0, np, t, e);
+    ld_buf<0>(S, op.aux0 + (int64_t)e * np, np, t, n);
+    ld_mat<0>(W, wv, 0, np, t, e);
+    svdwn_fwd_p(Pk, Wk, Mk, U, S, W, D, Bpw, n);
+    st_buf<0>(vbase(wv, k), Wk, np, t, e);
+    if (c.phase == PH_COEF) {
+        st_buf<0>(op.auxk + (int64_t)k * op.auxk_stride, Pk, np, t, e);
+    }
+}
+
 /*!
  * SVD-W.  Outputs (U, S, W).  Polar mode (U and S have no readers;
  * libsanm/oprs/linalg.cpp:529-550): hidden stack P_k, self-bias cache =
@@ -1327,6 +1604,11 @@ SANM_HD inline void op_svdw(const DOp& op, const ItemCtx& c) {
     const DVar &xv = c.var(x), &wv = c.var(ow);
     const int64_t np = c.np;
     const size_t t = c.t;
+    if (xv.d1 != 3) {
+        // general n: polar mode only (graph.cpp rejects the full mode)
+        op_svdw_n(op, c, xv.d1);
+        return;
+    }
     double U[9], S[3], W[9];
     if (c.phase == PH_EVAL) {
         double M[9];
