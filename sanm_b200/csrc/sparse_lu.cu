@@ -1384,20 +1384,25 @@ void SparseLU::factor(const double* vals_dev) {
                 }
                 {
                     LuScope ps{"lu_wide_row"};
-                    rt::for_each_block<W_GEMM_THREADS, WideCfg::MINB>(
-                            (size_t)L.wide_n * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
+                    rt::for_each_block<WidePanelCfg::THREADS, WidePanelCfg::MINB>(
+                            (size_t)L.wide_n * tiles, WidePanelCfg::THREADS,
+                            WidePanelCfg::SMEM,
                             WidePanelKernel<true>{I.fd.ptr(), list, kb, tiles});
                 }
                 {
                     LuScope ps{"lu_wide_gemm"};
-                    rt::for_each_block<W_GEMM_THREADS, WideCfg::MINB>(
-                            (size_t)L.wide_n * tiles * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
-                            WideGemmKernel{I.fd.ptr(), list, kb, tiles});
+                    const uint32_t tiles_m =
+                            (L.wide_max_nr + WideGemmCfg::TM - 1) / WideGemmCfg::TM;
+                    rt::for_each_block<WideGemmCfg::THREADS, WideGemmCfg::MINB>(
+                            (size_t)L.wide_n * tiles_m * tiles, WideGemmCfg::THREADS,
+                            WideGemmCfg::SMEM,
+                            WideGemmKernel{I.fd.ptr(), list, kb, tiles_m, tiles});
                 }
                 {
                     LuScope ps{"lu_wide_col"};
-                    rt::for_each_block<W_GEMM_THREADS, WideCfg::MINB>(
-                            (size_t)L.wide_n * tiles, W_GEMM_THREADS, W_GEMM_SMEM,
+                    rt::for_each_block<WidePanelCfg::THREADS, WidePanelCfg::MINB>(
+                            (size_t)L.wide_n * tiles, WidePanelCfg::THREADS,
+                            WidePanelCfg::SMEM,
                             WidePanelKernel<false>{I.fd.ptr(), list, kb, tiles});
                 }
             }

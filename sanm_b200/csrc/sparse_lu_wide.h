@@ -31,36 +31,46 @@ constexpr int WB = 128;  //!< pivots per superblock
 constexpr int WT = 128;  //!< tile edge of the panel / trailing GEMMs
 
 /*! Shape of the tile kernel: WM x WN warps, each MT x NT DMMA tiles of 8 x 8
- * (WM MT 8 = WN NT 8 = WT), K staged WK deep in STAGES buffers.
- * Shared-memory strides WT + 4 / WK + 4 (= 4 mod 16 doubles) make the fragment
- * loads of a half-warp hit 16 distinct 8-byte banks. */
-template <int WM_, int WN_, int WK_, int STAGES_, int MINB_>
+ * (tile = TM x WT with TM = WM MT 8 rows and WN NT 8 = WT columns), K staged WK
+ * deep in STAGES buffers.  Shared-memory strides TM + 4 / WK + 4 (= 4 mod 16
+ * doubles) make the fragment loads of a half-warp hit 16 distinct 8-byte
+ * banks. */
+template <int WM_, int WN_, int MT_, int NT_, int WK_, int STAGES_, int MINB_>
 struct WideCfgT {
-    static constexpr int WM = WM_, WN = WN_, WK = WK_, STAGES = STAGES_, MINB = MINB_;
-    static constexpr int MT = WT / 8 / WM, NT = WT / 8 / WN;
+    static constexpr int WM = WM_, WN = WN_, MT = MT_, NT = NT_, WK = WK_,
+                         STAGES = STAGES_, MINB = MINB_;
+    static constexpr int TM = WM * MT * 8;
     static constexpr int THREADS = 32 * WM * WN;
-    static constexpr int LDA = WT + 4, LDB = WK + 4;
+    static constexpr int LDA = TM + 4, LDB = WK + 4;
     static constexpr int STAGE_DOUBLES = WK * LDA + WT * LDB;
+#ifdef SANM_HOSTEMU
+    // the emulated tile keeps its product in the block's scratch
+    static constexpr size_t SMEM = (size_t)WT * WT * sizeof(double);
+#else
     static constexpr size_t SMEM = (size_t)STAGES * STAGE_DOUBLES * sizeof(double);
-    static_assert(WM * MT * 8 == WT && WN * NT * 8 == WT && WK % 4 == 0 &&
-                          (LDB % 16) == 4,
+#endif
+    static_assert(TM <= WT && WN * NT * 8 == WT && WK % 4 == 0 && (LDB % 16) == 4 &&
+                          (LDA % 16) == 4,
                   "tile shape");
 };
-//! 8 warps of 64 x 32, one CTA per SM (227 registers): 21.4 TFLOP/s on the
-//! trailing updates of the 1 M-tet cuboid (default)
-using WideCfgBig = WideCfgT<2, 4, 32, 2, 1>;
-//! 16 warps of 32 x 32 (a 128 x 128 FP64 accumulator tile is half of the SM's
-//! register file, so one CTA per SM either way), K staged 16 deep in 3 buffers:
-//! measured 8 % slower than WideCfgBig (19.8 TFLOP/s)
-using WideCfgDual = WideCfgT<4, 4, 16, 3, 1>;
-#ifndef SANM_WIDE_CFG
-#define SANM_WIDE_CFG WideCfgBig
+//! panels (128 x 128 outputs, K = 128): 8 warps of 64 x 32, one CTA per SM
+using WidePanelCfg = WideCfgT<2, 4, 8, 4, 32, 2, 1>;
+/*! trailing update.  Big (default): the same 128 x 128 tile, one CTA per SM
+ * (227 registers) -- 21.4 TFLOP/s on the 1 M-tet cuboid.
+ * Split: 64 x 128 tiles, 8 warps of 32 x 32, TWO CTAs per SM (126 registers,
+ * 2 x 106 KB of stages) so that one CTA's tile loads and stores run under the
+ * other's DMMAs.  Measured NOT faster (1.28 vs 1.25 s of trailing updates per
+ * factorisation of the 1 M-tet cuboid): a 32 x 32 warp tile needs 8 fragment
+ * loads per 16 DMMAs instead of 12 per 32, and ncu shows the shared-memory
+ * pipe taking what the overlap gives (mio_throttle 16 %, short scoreboard
+ * 10 % of the samples; profiles/r2_v_widegemm_split_ncu.txt).
+ * -DSANM_WIDE_GEMM_CFG=WideGemmSplit selects it. */
+using WideGemmBig = WideCfgT<2, 4, 8, 4, 32, 2, 1>;
+using WideGemmSplit = WideCfgT<2, 4, 4, 4, 32, 2, 2>;
+#ifndef SANM_WIDE_GEMM_CFG
+#define SANM_WIDE_GEMM_CFG WideGemmBig
 #endif
-using WideCfg = SANM_WIDE_CFG;
-constexpr size_t W_GEMM_SMEM =
-        WideCfg::SMEM > (size_t)WT * WT * sizeof(double) ? WideCfg::SMEM
-                                                         : (size_t)WT * WT * sizeof(double);
-constexpr int W_GEMM_THREADS = WideCfg::THREADS;
+using WideGemmCfg = SANM_WIDE_GEMM_CFG;
 
 enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
 
@@ -68,11 +78,11 @@ enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
  *   A(i, q) = Ap[q * lda + i]
  *   B(q, j) = Bp[j * ldb + (kperm ? kperm[q] : q)]
  *   C(i, j) = Cp[j * ldc + i]
- * m, n <= WT, k <= WB.  Entries with local row in [rs0, rs1) or local column
+ * m <= G::TM, n <= WT, k <= WB.  Entries with local row in [rs0, rs1) or local column
  * in [cs0, cs1) are not stored (the pivot rows / columns of the step).  C may
  * alias A or B (the panels are updated in place): every operand element is in
  * shared memory before the first store. */
-template <int MODE>
+template <class G, int MODE>
 SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
                                   uint64_t lda, const double* Bp, uint64_t ldb,
                                   const uint32_t* kperm, double* Cp, uint64_t ldc,
@@ -107,7 +117,6 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
         }
     }
 #else
-    using G = WideCfg;
     constexpr int WK = G::WK, MT = G::MT, NT = G::NT, LDA = G::LDA, LDB = G::LDB;
     double* sm = reinterpret_cast<double*>(c.smem);
     const int tid = c.tid, lane = tid & 31, warp = tid >> 5;
@@ -120,9 +129,9 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
         double* As = stage_ptr(s);
         double* Bs = As + WK * LDA;
         const uint32_t kk = k - k0 < (uint32_t)WK ? k - k0 : (uint32_t)WK;
-        // A chunk: WK columns (q) of WT rows; consecutive threads -> rows
-        for (int e = tid; e < WK * WT; e += G::THREADS) {
-            const uint32_t q = e / WT, i = e % WT;
+        // A chunk: WK columns (q) of TM rows; consecutive threads -> rows
+        for (int e = tid; e < WK * G::TM; e += G::THREADS) {
+            const uint32_t q = e / G::TM, i = e % G::TM;
             const bool ok = q < kk && i < m;
             const double* src = ok ? Ap + (uint64_t)(k0 + q) * lda + i : Ap;
             const uint32_t dst = (uint32_t)__cvta_generic_to_shared(As + q * LDA + i);
@@ -229,10 +238,10 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
 #endif
 }
 
-//! [a0, a1) intersected with the tile [t0, t0 + WT), in tile-local indices
+//! [a0, a1) intersected with the tile [t0, t0 + w), in tile-local indices
 SANM_HD inline void wide_clip(uint32_t a0, uint32_t a1, uint32_t t0, uint32_t* lo,
-                              uint32_t* hi) {
-    const uint32_t t1 = t0 + WT;
+                              uint32_t* hi, uint32_t w = WT) {
+    const uint32_t t1 = t0 + w;
     const uint32_t b0 = a0 > t0 ? a0 : t0, b1 = a1 < t1 ? a1 : t1;
     if (b0 < b1) {
         *lo = b0 - t0;
@@ -415,38 +424,39 @@ struct WidePanelKernel {
         double* D = f.F + (uint64_t)kb * f.nr + kb;
         if (ROW) {
             double* R = f.F + (uint64_t)t0 * f.nr + kb;  // rows kb.., columns t0..
-            wide_gemm_tile<W_SET>(c, D, f.nr, R, f.nr, f.lperm, R, f.nr, wb, ext, wb,
+            wide_gemm_tile<WidePanelCfg, W_SET>(c, D, f.nr, R, f.nr, f.lperm, R, f.nr, wb, ext, wb,
                                   0, 0, s0, s1);
         } else {
             double* C = f.F + (uint64_t)kb * f.nr + t0;  // rows t0.., columns kb..
-            wide_gemm_tile<W_SETNEG>(c, C, f.nr, D, f.nr, nullptr, C, f.nr, ext, wb,
+            wide_gemm_tile<WidePanelCfg, W_SETNEG>(c, C, f.nr, D, f.nr, nullptr, C, f.nr, ext, wb,
                                      wb, s0, s1, 0, 0);
         }
     }
 };
 
-//! F[Q,Q] -= F[Q,P] R' on one 128 x 128 tile
+//! F[Q,Q] -= F[Q,P] R' on one TM x 128 tile (tiles_m x tiles_n tiles per front)
 struct WideGemmKernel {
+    using G = WideGemmCfg;
     const FrontD* fronts;
     const uint32_t* list;
-    uint32_t kb, tiles;
+    uint32_t kb, tiles_m, tiles_n;
     SANM_D FrontD pre(const rt::BlockCtx& c) const {
-        return fronts[list[c.bid / ((size_t)tiles * tiles)]];
+        return fronts[list[c.bid / ((size_t)tiles_m * tiles_n)]];
     }
     SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
-        const uint32_t t = (uint32_t)(c.bid % ((size_t)tiles * tiles));
-        const uint32_t i0 = (t % tiles) * WT, j0 = (t / tiles) * WT;
+        const uint32_t t = (uint32_t)(c.bid % ((size_t)tiles_m * tiles_n));
+        const uint32_t i0 = (t % tiles_m) * G::TM, j0 = (t / tiles_m) * WT;
         if (kb >= f.nc || i0 >= f.nr || j0 >= f.nr) return;
         const uint32_t wb = f.nc - kb < (uint32_t)WB ? f.nc - kb : (uint32_t)WB;
-        const uint32_t mi = f.nr - i0 < (uint32_t)WT ? f.nr - i0 : (uint32_t)WT;
+        const uint32_t mi = f.nr - i0 < (uint32_t)G::TM ? f.nr - i0 : (uint32_t)G::TM;
         const uint32_t nj = f.nr - j0 < (uint32_t)WT ? f.nr - j0 : (uint32_t)WT;
         uint32_t rs0, rs1, cs0, cs1;
-        wide_clip(kb, kb + wb, i0, &rs0, &rs1);
+        wide_clip(kb, kb + wb, i0, &rs0, &rs1, G::TM);
         wide_clip(kb, kb + wb, j0, &cs0, &cs1);
         if (rs1 - rs0 == mi || cs1 - cs0 == nj) return;  // nothing to store
-        wide_gemm_tile<W_SUB>(c, f.F + (uint64_t)kb * f.nr + i0, f.nr,
-                              f.F + (uint64_t)j0 * f.nr + kb, f.nr, nullptr,
-                              f.F + (uint64_t)j0 * f.nr + i0, f.nr, mi, nj, wb, rs0,
-                              rs1, cs0, cs1);
+        wide_gemm_tile<G, W_SUB>(c, f.F + (uint64_t)kb * f.nr + i0, f.nr,
+                                 f.F + (uint64_t)j0 * f.nr + kb, f.nr, nullptr,
+                                 f.F + (uint64_t)j0 * f.nr + i0, f.nr, mi, nj, wb, rs0,
+                                 rs1, cs0, cs1);
     }
 };
