@@ -1391,12 +1391,27 @@ void SparseLU::factor(const double* vals_dev) {
                 }
                 {
                     LuScope ps{"lu_wide_gemm"};
-                    const uint32_t tiles_m =
-                            (L.wide_max_nr + WideGemmCfg::TM - 1) / WideGemmCfg::TM;
-                    rt::for_each_block<WideGemmCfg::THREADS, WideGemmCfg::MINB>(
-                            (size_t)L.wide_n * tiles_m * tiles, WideGemmCfg::THREADS,
-                            WideGemmCfg::SMEM,
-                            WideGemmKernel{I.fd.ptr(), list, kb, tiles_m, tiles});
+                    const int fast = getenv("SANM_LU_WIDE_SLOW") == nullptr;
+                    auto gemm = [&](auto cfg) {
+                        using G = decltype(cfg);
+                        const uint32_t tiles_m = (L.wide_max_nr + G::TM - 1) / G::TM;
+                        const uint32_t tiles_n = (L.wide_max_nr + G::TN - 1) / G::TN;
+                        rt::for_each_block<G::THREADS, G::MINB>(
+                                (size_t)L.wide_n * tiles_m * tiles_n, G::THREADS, G::SMEM,
+                                WideGemmKernelT<G>{I.fd.ptr(), list, kb, tiles_m, tiles_n,
+                                                   fast});
+                    };
+                    switch (wide_gemm_cfg()) {
+                        case 1:
+                            gemm(WideGemmSplit{});
+                            break;
+                        case 2:
+                            gemm(WideGemmHalfN{});
+                            break;
+                        default:
+                            gemm(WideGemmBig{});
+                            break;
+                    }
                 }
                 {
                     LuScope ps{"lu_wide_col"};

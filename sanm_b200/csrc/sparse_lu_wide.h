@@ -27,11 +27,14 @@
  */
 #pragma once
 
+#ifndef SANM_WIDE_GEMM_DEFAULT
+#define SANM_WIDE_GEMM_DEFAULT 0
+#endif
 constexpr int WB = 128;  //!< pivots per superblock
 constexpr int WT = 128;  //!< tile edge of the panel / trailing GEMMs
 
 /*! Shape of the tile kernel: WM x WN warps, each MT x NT DMMA tiles of 8 x 8
- * (tile = TM x WT with TM = WM MT 8 rows and WN NT 8 = WT columns), K staged WK
+ * (tile = TM x TN with TM = WM MT 8 rows and TN = WN NT 8 columns), K staged WK
  * deep in STAGES buffers.  Shared-memory strides TM + 4 / WK + 4 (= 4 mod 16
  * doubles) make the fragment loads of a half-warp hit 16 distinct 8-byte
  * banks. */
@@ -39,38 +42,47 @@ template <int WM_, int WN_, int MT_, int NT_, int WK_, int STAGES_, int MINB_>
 struct WideCfgT {
     static constexpr int WM = WM_, WN = WN_, MT = MT_, NT = NT_, WK = WK_,
                          STAGES = STAGES_, MINB = MINB_;
-    static constexpr int TM = WM * MT * 8;
+    static constexpr int TM = WM * MT * 8, TN = WN * NT * 8;
     static constexpr int THREADS = 32 * WM * WN;
     static constexpr int LDA = TM + 4, LDB = WK + 4;
-    static constexpr int STAGE_DOUBLES = WK * LDA + WT * LDB;
+    static constexpr int STAGE_DOUBLES = WK * LDA + TN * LDB;
 #ifdef SANM_HOSTEMU
     // the emulated tile keeps its product in the block's scratch
     static constexpr size_t SMEM = (size_t)WT * WT * sizeof(double);
 #else
     static constexpr size_t SMEM = (size_t)STAGES * STAGE_DOUBLES * sizeof(double);
 #endif
-    static_assert(TM <= WT && WN * NT * 8 == WT && WK % 4 == 0 && (LDB % 16) == 4 &&
+    static_assert(TM <= WT && TN <= WT && WK % 4 == 0 && (LDB % 16) == 4 &&
                           (LDA % 16) == 4,
                   "tile shape");
 };
 //! panels (128 x 128 outputs, K = 128): 8 warps of 64 x 32, one CTA per SM
 using WidePanelCfg = WideCfgT<2, 4, 8, 4, 32, 2, 1>;
-/*! trailing update.  Big (default): the same 128 x 128 tile, one CTA per SM
- * (227 registers) -- 21.4 TFLOP/s on the 1 M-tet cuboid.
- * Split: 64 x 128 tiles, 8 warps of 32 x 32, TWO CTAs per SM (126 registers,
- * 2 x 106 KB of stages) so that one CTA's tile loads and stores run under the
- * other's DMMAs.  Measured NOT faster (1.28 vs 1.25 s of trailing updates per
- * factorisation of the 1 M-tet cuboid): a 32 x 32 warp tile needs 8 fragment
- * loads per 16 DMMAs instead of 12 per 32, and ncu shows the shared-memory
- * pipe taking what the overlap gives (mio_throttle 16 %, short scoreboard
- * 10 % of the samples; profiles/r2_v_widegemm_split_ncu.txt).
- * -DSANM_WIDE_GEMM_CFG=WideGemmSplit selects it. */
+/*! trailing update, selectable at run time (SANM_LU_WIDE_CFG).  Measured on the
+ * 1.08 M-tet cuboid, trailing updates per factorisation, all with the fast
+ * interior tiles below (profiles/r2_x_widegemm_fast_ncu.txt):
+ *   big   (default) 128 x 128, 8 warps of 64 x 32, one CTA per SM   1.134 s
+ *   split 64 x 128, 8 warps of 32 x 32, two CTAs per SM             1.258 s
+ *   halfn 128 x 64, 4 warps of 64 x 32, two CTAs per SM             1.303 s
+ * Two CTAs per SM overlap one tile's loads and stores with the other's DMMAs,
+ * but move 25 % more bytes per flop through L2 (0.152 vs 0.122 B/flop) and
+ * lose more than the overlap gives. */
 using WideGemmBig = WideCfgT<2, 4, 8, 4, 32, 2, 1>;
 using WideGemmSplit = WideCfgT<2, 4, 4, 4, 32, 2, 2>;
-#ifndef SANM_WIDE_GEMM_CFG
-#define SANM_WIDE_GEMM_CFG WideGemmBig
-#endif
-using WideGemmCfg = SANM_WIDE_GEMM_CFG;
+//! HalfN: 128 x 64 tiles, FOUR warps of 64 x 32 (the warp tile and fragment-load
+//! ratio of Big), two 128-thread CTAs per SM that run out of phase
+using WideGemmHalfN = WideCfgT<2, 2, 8, 4, 32, 2, 2>;
+//! which of the three runs: SANM_LU_WIDE_CFG = big | split | halfn
+inline int wide_gemm_cfg() {
+    static const int v = [] {
+        const char* e = getenv("SANM_LU_WIDE_CFG");
+        if (e && !strcmp(e, "split")) return 1;
+        if (e && !strcmp(e, "halfn")) return 2;
+        if (e && !strcmp(e, "big")) return 0;
+        return SANM_WIDE_GEMM_DEFAULT;
+    }();
+    return v;
+}
 
 enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
 
@@ -78,7 +90,7 @@ enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
  *   A(i, q) = Ap[q * lda + i]
  *   B(q, j) = Bp[j * ldb + (kperm ? kperm[q] : q)]
  *   C(i, j) = Cp[j * ldc + i]
- * m <= G::TM, n <= WT, k <= WB.  Entries with local row in [rs0, rs1) or local column
+ * m <= G::TM, n <= G::TN, k <= WB.  Entries with local row in [rs0, rs1) or local column
  * in [cs0, cs1) are not stored (the pivot rows / columns of the step).  C may
  * alias A or B (the panels are updated in place): every operand element is in
  * shared memory before the first store. */
@@ -139,8 +151,8 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
                          "l"(src), "r"(ok ? 8 : 0)
                          : "memory");
         }
-        // B chunk: WT columns (j) of WK rows (q); consecutive threads -> q
-        for (int e = tid; e < WT * WK; e += G::THREADS) {
+        // B chunk: TN columns (j) of WK rows (q); consecutive threads -> q
+        for (int e = tid; e < G::TN * WK; e += G::THREADS) {
             const uint32_t j = e / WK, q = e % WK;
             const bool ok = q < kk && j < n;
             const uint32_t qq = ok ? (kperm ? kperm[k0 + q] : k0 + q) : 0;
@@ -237,6 +249,146 @@ SANM_D inline void wide_gemm_tile(const rt::BlockCtx& c, const double* Ap,
     }
 #endif
 }
+
+#ifndef SANM_HOSTEMU
+/*! Interior tiles of the trailing update: C(TM x TN) -= A(TM x WB) B(WB x TN),
+ * full tile, K = WB, no pivot rows or columns inside.  Same arithmetic as
+ * wide_gemm_tile<G, W_SUB> bit for bit, with the instruction count per DMMA cut
+ * down -- which is what the tile time is made of: with two warps per scheduler
+ * a warp's non-DMMA instructions are not hidden by anything (ncu on the
+ * generic tile: 5,858 warp instructions per 1,024 DMMAs, 9 cycles per issued
+ * instruction, tensor pipe busy 59 % = 21.9 TFLOP/s; per tile
+ * 2 x 1,024 x 16 cycles of DMMA + 4,834 x 4.7 cycles of everything else).
+ *   - operand stages: every thread owns one row (A) / one k index (B) and walks
+ *     the columns with pointer increments: no index arithmetic, no predicates;
+ *   - the accumulators start from -C and the MMAs run with +A (no sign flip
+ *     per fragment; -(-C + A B) = C - A B exactly, rounding is symmetric);
+ *   - C is read and written through eight column pointers per thread with
+ *     immediate offsets, as global (not generic) accesses. */
+template <class G>
+SANM_D inline void wide_gemm_tile_fast(const rt::BlockCtx& c,
+                                       const double* __restrict__ Ap, uint64_t lda,
+                                       const double* __restrict__ Bp, uint64_t ldb,
+                                       double* __restrict__ Cp, uint64_t ldc) {
+    constexpr int WK = G::WK, MT = G::MT, NT = G::NT, LDA = G::LDA, LDB = G::LDB;
+    constexpr int TM = G::TM, TN = G::TN, THREADS = G::THREADS;
+    constexpr int NCHUNK = WB / WK;
+    static_assert(THREADS % TM == 0 && THREADS % WK == 0 && WB % WK == 0, "stage walk");
+    constexpr int A_QSTEP = THREADS / TM, A_IT = WK / A_QSTEP;
+    constexpr int B_JSTEP = THREADS / WK, B_IT = TN / B_JSTEP;
+    constexpr uint32_t STAGE_BYTES = G::STAGE_DOUBLES * sizeof(double);
+    const int tid = c.tid, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp % G::WM, wn = warp / G::WM;
+    const int g = lane >> 2, t4 = lane & 3;
+    double* sm = reinterpret_cast<double*>(c.smem);
+    const uint32_t sm0 = (uint32_t)__cvta_generic_to_shared(sm);
+
+    const int ai = tid % TM, aq = tid / TM;
+    const int bq = tid % WK, bj = tid / WK;
+    const double* asrc = Ap + (uint64_t)aq * lda + ai;
+    const double* bsrc = Bp + (uint64_t)bj * ldb + bq;
+    const uint32_t adst0 = sm0 + (uint32_t)(aq * LDA + ai) * 8u;
+    const uint32_t bdst0 = sm0 + (uint32_t)(WK * LDA + bj * LDB + bq) * 8u;
+    // The copies of a stage are issued in KS = WK / 4 parts, one part after the
+    // DMMAs of each k-step of the chunk before: 32 copies in a row per thread
+    // fill the load/store queue and stall the warp -- one of only two DMMA
+    // issuers of its scheduler (ncu: lg_throttle 17 % of the samples).
+    constexpr int KS = WK / 4;
+    static_assert(A_IT % KS == 0 && B_IT % KS == 0, "stage parts");
+    constexpr int A_PART = A_IT / KS, B_PART = B_IT / KS;
+    const double* a_run = asrc;
+    const double* b_run = bsrc;
+    uint32_t ad_run = adst0, bd_run = bdst0;
+    auto stage_begin = [&](int s, int kc) {
+        a_run = asrc + (uint64_t)(kc * WK) * lda;
+        b_run = bsrc + kc * WK;
+        ad_run = adst0 + (uint32_t)s * STAGE_BYTES;
+        bd_run = bdst0 + (uint32_t)s * STAGE_BYTES;
+    };
+    auto stage_part = [&]() {
+#pragma unroll
+        for (int it = 0; it < A_PART; ++it) {
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ad_run),
+                         "l"(a_run)
+                         : "memory");
+            a_run += (uint64_t)A_QSTEP * lda;
+            ad_run += (uint32_t)(A_QSTEP * LDA) * 8u;
+        }
+#pragma unroll
+        for (int it = 0; it < B_PART; ++it) {
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(bd_run),
+                         "l"(b_run)
+                         : "memory");
+            b_run += (uint64_t)B_JSTEP * ldb;
+            bd_run += (uint32_t)(B_JSTEP * LDB) * 8u;
+        }
+    };
+    auto commit = [] { asm volatile("cp.async.commit_group;" ::: "memory"); };
+
+#pragma unroll
+    for (int s = 0; s < G::STAGES - 1; ++s) {
+        if (s < NCHUNK) {
+            stage_begin(s, s);
+#pragma unroll
+            for (int part = 0; part < KS; ++part) stage_part();
+        }
+        commit();
+    }
+    double acc[MT][NT][2];
+    double* cbase = Cp + (uint64_t)(wn * (NT * 8) + 2 * t4) * ldc + wm * (MT * 8) + g;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const double* col = cbase + (uint64_t)(nt * 8 + h) * ldc;
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) acc[mt][nt][h] = -__ldcg(col + mt * 8);
+        }
+    }
+#pragma unroll 1
+    for (int kc = 0; kc < NCHUNK; ++kc) {
+        // chunk kc is the oldest group in flight: wait for it alone
+        asm volatile("cp.async.wait_group %0;" ::"n"(G::STAGES - 2) : "memory");
+        __syncthreads();  // ... and every warp is done with the buffer refilled below
+        const bool more = kc + G::STAGES - 1 < NCHUNK;
+        if (more) stage_begin((kc + G::STAGES - 1) % G::STAGES, kc + G::STAGES - 1);
+        const double* As = sm + (size_t)(kc % G::STAGES) * G::STAGE_DOUBLES +
+                           wm * (MT * 8) + g + t4 * LDA;
+        const double* Bs = sm + (size_t)(kc % G::STAGES) * G::STAGE_DOUBLES + WK * LDA +
+                           (wn * (NT * 8) + g) * LDB + t4;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+            double a[MT], b[NT];
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) a[mt] = As[ks * 4 * LDA + mt * 8];
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) b[nt] = Bs[nt * 8 * LDB + ks * 4];
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    asm volatile(
+                            "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 "
+                            "{%0,%1}, {%2}, {%3}, {%0,%1};"
+                            : "+d"(acc[mt][nt][0]), "+d"(acc[mt][nt][1])
+                            : "d"(a[mt]), "d"(b[nt]));
+                }
+            }
+            if (more) stage_part();
+        }
+        commit();
+    }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            double* col = cbase + (uint64_t)(nt * 8 + h) * ldc;
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) __stcg(col + mt * 8, -acc[mt][nt][h]);
+        }
+    }
+}
+#endif
 
 //! [a0, a1) intersected with the tile [t0, t0 + w), in tile-local indices
 SANM_HD inline void wide_clip(uint32_t a0, uint32_t a1, uint32_t t0, uint32_t* lo,
@@ -434,26 +586,36 @@ struct WidePanelKernel {
     }
 };
 
-//! F[Q,Q] -= F[Q,P] R' on one TM x 128 tile (tiles_m x tiles_n tiles per front)
-struct WideGemmKernel {
-    using G = WideGemmCfg;
+//! F[Q,Q] -= F[Q,P] R' on one TM x TN tile (tiles_m x tiles_n tiles per front)
+template <class G>
+struct WideGemmKernelT {
     const FrontD* fronts;
     const uint32_t* list;
     uint32_t kb, tiles_m, tiles_n;
+    int wide_fast;  //!< interior tiles take wide_gemm_tile_fast (SANM_LU_WIDE_SLOW=1: off)
     SANM_D FrontD pre(const rt::BlockCtx& c) const {
         return fronts[list[c.bid / ((size_t)tiles_m * tiles_n)]];
     }
     SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
         const uint32_t t = (uint32_t)(c.bid % ((size_t)tiles_m * tiles_n));
-        const uint32_t i0 = (t % tiles_m) * G::TM, j0 = (t / tiles_m) * WT;
+        const uint32_t i0 = (t % tiles_m) * G::TM, j0 = (t / tiles_m) * G::TN;
         if (kb >= f.nc || i0 >= f.nr || j0 >= f.nr) return;
         const uint32_t wb = f.nc - kb < (uint32_t)WB ? f.nc - kb : (uint32_t)WB;
         const uint32_t mi = f.nr - i0 < (uint32_t)G::TM ? f.nr - i0 : (uint32_t)G::TM;
-        const uint32_t nj = f.nr - j0 < (uint32_t)WT ? f.nr - j0 : (uint32_t)WT;
+        const uint32_t nj = f.nr - j0 < (uint32_t)G::TN ? f.nr - j0 : (uint32_t)G::TN;
         uint32_t rs0, rs1, cs0, cs1;
         wide_clip(kb, kb + wb, i0, &rs0, &rs1, G::TM);
-        wide_clip(kb, kb + wb, j0, &cs0, &cs1);
+        wide_clip(kb, kb + wb, j0, &cs0, &cs1, G::TN);
         if (rs1 - rs0 == mi || cs1 - cs0 == nj) return;  // nothing to store
+#ifndef SANM_HOSTEMU
+        if (wide_fast && wb == (uint32_t)WB && mi == (uint32_t)G::TM &&
+            nj == (uint32_t)G::TN && rs0 == rs1 && cs0 == cs1) {
+            wide_gemm_tile_fast<G>(c, f.F + (uint64_t)kb * f.nr + i0, f.nr,
+                                   f.F + (uint64_t)j0 * f.nr + kb, f.nr,
+                                   f.F + (uint64_t)j0 * f.nr + i0, f.nr);
+            return;
+        }
+#endif
         wide_gemm_tile<G, W_SUB>(c, f.F + (uint64_t)kb * f.nr + i0, f.nr,
                                  f.F + (uint64_t)j0 * f.nr + kb, f.nr, nullptr,
                                  f.F + (uint64_t)j0 * f.nr + i0, f.nr, mi, nj, wb, rs0,

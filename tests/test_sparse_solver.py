@@ -160,3 +160,26 @@ def test_large_system_gpu(cuda_impl, monkeypatch):
         r = A @ x - b
         scale = abs(A).sum(axis=1).max() * np.abs(x).max() + np.abs(b).max()
         assert np.abs(r).max() <= 1e-12 * scale
+
+
+@pytest.mark.gpu
+def test_wide_gemm_fast_tiles_bitwise_gpu(cuda_impl, monkeypatch):
+    """interior tiles of the rank-128 trailing update take a leaner code path
+    (sparse_lu_wide.h wide_gemm_tile_fast: accumulators start from -C, +A in the
+    MMAs); it must reproduce the generic tile bit for bit"""
+    rng = np.random.default_rng(23)
+    A = grid_matrix(30, 30, 30, rng, nonsym=0.2)
+    n = A.shape[0]
+    b = rng.uniform(-1, 1, n)
+    xs = []
+    for slow in (False, True):
+        if slow:
+            monkeypatch.setenv("SANM_LU_WIDE_SLOW", "1")
+        else:
+            monkeypatch.delenv("SANM_LU_WIDE_SLOW", raising=False)
+        xs.append(build(cuda_impl, A).prepare().solve(b))
+    assert np.array_equal(xs[0], xs[1])
+    r = A @ xs[0] - b
+    scale = abs(A).sum(axis=1).max() * np.abs(xs[0]).max() + np.abs(b).max()
+    assert np.abs(r).max() <= 1e-12 * scale
+

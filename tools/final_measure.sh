@@ -14,9 +14,9 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file $O/launches.csv python bench.py $SHORT > $O/ncu_launches.log 2>&1
 python bench.py $SHORT > /dev/null 2>&1 && \
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum \
-    --clock-control none -k regex:StepKernel -s 19 -c 19 --csv \
+    --clock-control none --kernel-name-base demangled -k regex:StepKernel -s 19 -c 19 --csv \
     --log-file $O/step_dram.csv python bench.py $SHORT > $O/ncu_step_dram.log 2>&1
 python bench.py $SHORT > /dev/null 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:StepKernel -s 29 -c 1 -f \
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:StepKernel -s 29 -c 1 -f \
     -o $O/step_full python bench.py $SHORT > $O/ncu_step_full.log 2>&1
 ls -la $O | tail -12
