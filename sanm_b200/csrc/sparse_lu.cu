@@ -1408,6 +1408,21 @@ void SparseLU::factor(const double* vals_dev) {
                         case 2:
                             gemm(WideGemmHalfN{});
                             break;
+                        case 3:
+                            gemm(WideGemmBig3{});
+                            break;
+#ifndef SANM_HOSTEMU
+                        case 4: {
+                            const uint64_t ntile = (uint64_t)L.wide_n * tiles * tiles;
+                            const uint64_t nsm = (uint64_t)rt::sm_count();
+                            rt::for_each_block<WidePersist::THREADS, 1>(
+                                    (size_t)(ntile < nsm ? ntile : nsm), WidePersist::THREADS,
+                                    WidePersist::SMEM,
+                                    WideGemmPersistKernel{I.fd.ptr(), list, kb, tiles,
+                                                          L.wide_n});
+                            break;
+                        }
+#endif
                         default:
                             gemm(WideGemmBig{});
                             break;

@@ -28,7 +28,7 @@
 #pragma once
 
 #ifndef SANM_WIDE_GEMM_DEFAULT
-#define SANM_WIDE_GEMM_DEFAULT 0
+#define SANM_WIDE_GEMM_DEFAULT 4
 #endif
 constexpr int WB = 128;  //!< pivots per superblock
 constexpr int WT = 128;  //!< tile edge of the panel / trailing GEMMs
@@ -61,27 +61,32 @@ using WidePanelCfg = WideCfgT<2, 4, 8, 4, 32, 2, 1>;
 /*! trailing update, selectable at run time (SANM_LU_WIDE_CFG).  Measured on the
  * 1.08 M-tet cuboid, trailing updates per factorisation, all with the fast
  * interior tiles below (profiles/r2_x_widegemm_fast_ncu.txt):
- *   big   (default) 128 x 128, 8 warps of 64 x 32, one CTA per SM   1.134 s
- *   split 64 x 128, 8 warps of 32 x 32, two CTAs per SM             1.258 s
- *   halfn 128 x 64, 4 warps of 64 x 32, two CTAs per SM             1.303 s
+ *   persist (default) 128 x 128, one persistent CTA per SM, next tile's C
+ *           and first stage prefetched under the DMMAs (WideGemmPersistKernel) 1.032 s
+ *   big     128 x 128, 8 warps of 64 x 32, one CTA per SM, two 32-deep stages   1.134 s
+ *   big3    the same with three stages (a larger prologue per tile)            1.385 s
+ *   split   64 x 128, 8 warps of 32 x 32, two CTAs per SM                       1.258 s
+ *   halfn   128 x 64, 4 warps of 64 x 32, two CTAs per SM                       1.303 s
  * Two CTAs per SM overlap one tile's loads and stores with the other's DMMAs,
  * but move 25 % more bytes per flop through L2 (0.152 vs 0.122 B/flop) and
  * lose more than the overlap gives. */
 using WideGemmBig = WideCfgT<2, 4, 8, 4, 32, 2, 1>;
 using WideGemmSplit = WideCfgT<2, 4, 4, 4, 32, 2, 2>;
+//! Big with three stages (212 KB): a whole chunk of slack for the copies
+using WideGemmBig3 = WideCfgT<2, 4, 8, 4, 32, 3, 1>;
 //! HalfN: 128 x 64 tiles, FOUR warps of 64 x 32 (the warp tile and fragment-load
 //! ratio of Big), two 128-thread CTAs per SM that run out of phase
 using WideGemmHalfN = WideCfgT<2, 2, 8, 4, 32, 2, 2>;
 //! which of the three runs: SANM_LU_WIDE_CFG = big | split | halfn
 inline int wide_gemm_cfg() {
-    static const int v = [] {
-        const char* e = getenv("SANM_LU_WIDE_CFG");
-        if (e && !strcmp(e, "split")) return 1;
-        if (e && !strcmp(e, "halfn")) return 2;
-        if (e && !strcmp(e, "big")) return 0;
-        return SANM_WIDE_GEMM_DEFAULT;
-    }();
-    return v;
+    // read per call: tests switch it inside one process
+    const char* e = getenv("SANM_LU_WIDE_CFG");
+    if (e && !strcmp(e, "big")) return 0;
+    if (e && !strcmp(e, "split")) return 1;
+    if (e && !strcmp(e, "halfn")) return 2;
+    if (e && !strcmp(e, "big3")) return 3;
+    if (e && !strcmp(e, "persist")) return 4;
+    return SANM_WIDE_GEMM_DEFAULT;
 }
 
 enum WideMode { W_SUB = 0, W_SET = 1, W_SETNEG = 2 };
@@ -556,6 +561,265 @@ constexpr size_t W_DIAG_SMEM =
 constexpr size_t W_DIAG_SMEM =
         ((size_t)WB * WB + 32 * 32 + 2 * (size_t)WB * 32 + 64) * sizeof(double) +
         (32 + WB) * sizeof(uint32_t);
+#endif
+
+#ifndef SANM_HOSTEMU
+/*! Persistent form of the trailing update: one CTA per SM walks the tiles of
+ * the launch (t = bid, bid + grid, ...) and, while the DMMAs of one interior
+ * tile run, brings in the NEXT tile's C (128 KB, into a shared-memory buffer)
+ * and its first operand stage.  What a tile costs beyond its DMMAs is the data
+ * that has to arrive before the first of them (C + one stage; a third stage in
+ * the prologue made the plain kernel 22 % slower) -- here that wait belongs to
+ * the previous tile.  16-deep stages leave room for the C buffer:
+ * 2 x 36.5 KB + 130 KB.  Edge tiles and tiles that contain pivot rows or
+ * columns go through the generic tile function (nothing prefetched across
+ * them).  Arithmetic is that of wide_gemm_tile_fast, bit for bit.
+ * The copies are spread over the k-steps (8 A, 8 B, 4 C, 4 C per thread and
+ * chunk): issuing a chunk's 16 stage copies in one burst cost 12 % (the
+ * load/store queue fills and stalls one of the two DMMA issuers). */
+struct WidePersist {
+    static constexpr int WK = 16, KS = WK / 4, NCHUNK = WB / WK, THREADS = 256;
+    static constexpr int WM = 2, WN = 4, MT = 8, NT = 4;
+    static constexpr int LDA = WT + 4, LDB = WK + 4, LDC = WT + 2;
+    static constexpr int STAGE_DOUBLES = WK * LDA + WT * LDB;
+    static constexpr int CBUF_DOUBLES = WT * LDC;
+    static constexpr size_t SMEM =
+            (size_t)(2 * STAGE_DOUBLES + CBUF_DOUBLES) * sizeof(double);
+    static constexpr int A_IT = WK * WT / THREADS, B_IT = WT * WK / THREADS;  // 8, 8
+    static constexpr int C_IT = WT * WT / THREADS;                            // 64
+    static_assert(SMEM >= WideGemmBig::SMEM && (LDB % 16) == 4 && (NCHUNK % 2) == 0, "layout");
+};
+
+struct WideGemmPersistKernel {
+    using P = WidePersist;
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb, tiles, nfront;
+
+    struct Tile {
+        int kind;  //!< 0 nothing to do, 1 interior (fast), 2 generic
+        double* F;
+        uint32_t nr, nc, i0, j0;
+    };
+    SANM_D Tile describe(uint64_t t, uint32_t& cached_fi, FrontD& cached) const {
+        const uint64_t per = (uint64_t)tiles * tiles;
+        const uint32_t fi = (uint32_t)(t / per), idx = (uint32_t)(t % per);
+        if (fi != cached_fi) {
+            cached = fronts[list[fi]];
+            cached_fi = fi;
+        }
+        Tile d;
+        d.F = cached.F;
+        d.nr = cached.nr;
+        d.nc = cached.nc;
+        d.i0 = (idx % tiles) * WT;
+        d.j0 = (idx / tiles) * WT;
+        d.kind = 0;
+        if (kb >= d.nc || d.i0 >= d.nr || d.j0 >= d.nr) return d;
+        const uint32_t wb = d.nc - kb < (uint32_t)WB ? d.nc - kb : (uint32_t)WB;
+        const uint32_t mi = d.nr - d.i0 < (uint32_t)WT ? d.nr - d.i0 : (uint32_t)WT;
+        const uint32_t nj = d.nr - d.j0 < (uint32_t)WT ? d.nr - d.j0 : (uint32_t)WT;
+        uint32_t rs0, rs1, cs0, cs1;
+        wide_clip(kb, kb + wb, d.i0, &rs0, &rs1);
+        wide_clip(kb, kb + wb, d.j0, &cs0, &cs1);
+        if (rs1 - rs0 == mi || cs1 - cs0 == nj) return d;
+        d.kind = (wb == (uint32_t)WB && mi == (uint32_t)WT && nj == (uint32_t)WT &&
+                  rs0 == rs1 && cs0 == cs1)
+                         ? 1
+                         : 2;
+        return d;
+    }
+    SANM_D void generic(const rt::BlockCtx& c, const Tile& d) const {
+        const uint32_t wb = d.nc - kb < (uint32_t)WB ? d.nc - kb : (uint32_t)WB;
+        const uint32_t mi = d.nr - d.i0 < (uint32_t)WT ? d.nr - d.i0 : (uint32_t)WT;
+        const uint32_t nj = d.nr - d.j0 < (uint32_t)WT ? d.nr - d.j0 : (uint32_t)WT;
+        uint32_t rs0, rs1, cs0, cs1;
+        wide_clip(kb, kb + wb, d.i0, &rs0, &rs1);
+        wide_clip(kb, kb + wb, d.j0, &cs0, &cs1);
+        wide_gemm_tile<WideGemmBig, W_SUB>(c, d.F + (uint64_t)kb * d.nr + d.i0, d.nr,
+                                           d.F + (uint64_t)d.j0 * d.nr + kb, d.nr, nullptr,
+                                           d.F + (uint64_t)d.j0 * d.nr + d.i0, d.nr, mi, nj,
+                                           wb, rs0, rs1, cs0, cs1);
+    }
+    SANM_D void operator()(const rt::BlockCtx& c) const;
+};
+#endif
+
+#ifndef SANM_HOSTEMU
+SANM_D inline void WideGemmPersistKernel::operator()(const rt::BlockCtx& c) const {
+    constexpr int WK = P::WK, NCHUNK = P::NCHUNK, MT = P::MT, NT = P::NT;
+    constexpr int LDA = P::LDA, LDB = P::LDB, LDC = P::LDC;
+    constexpr uint32_t STAGE_BYTES = P::STAGE_DOUBLES * sizeof(double);
+    const int tid = c.tid, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp % P::WM, wn = warp / P::WM;
+    const int g = lane >> 2, t4 = lane & 3;
+    double* sm = reinterpret_cast<double*>(c.smem);
+    double* cbuf = sm + 2 * P::STAGE_DOUBLES;
+    const uint32_t sm0 = (uint32_t)__cvta_generic_to_shared(sm);
+    // the copies every thread owns: A row ai, k columns aq, aq + 2, ...; B k index
+    // bq, columns bj, bj + 16, ...; C row ai, columns aq, aq + 2, ...
+    const int ai = tid % WT, aq = tid / WT;
+    const int bq = tid % WK, bj = tid / WK;
+    const uint32_t adst0 = sm0 + (uint32_t)(aq * LDA + ai) * 8u;
+    const uint32_t bdst0 = sm0 + (uint32_t)(WK * LDA + bj * LDB + bq) * 8u;
+    const uint32_t cdst0 = sm0 + 2u * STAGE_BYTES + (uint32_t)(aq * LDC + ai) * 8u;
+    const double* As0 = sm + wm * (MT * 8) + g + t4 * LDA;
+    const double* Bs0 = sm + WK * LDA + (wn * (NT * 8) + g) * LDB + t4;
+    const double* Cs0 = cbuf + (wn * (NT * 8) + 2 * t4) * LDC + wm * (MT * 8) + g;
+    auto cp8 = [](uint32_t dst, const double* src) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src)
+                     : "memory");
+    };
+    auto commit = [] { asm volatile("cp.async.commit_group;" ::: "memory"); };
+    auto wait_all = [] { asm volatile("cp.async.wait_group 0;" ::: "memory"); };
+
+    const uint64_t total = (uint64_t)nfront * tiles * tiles;
+    uint32_t cfi = ~0u;
+    FrontD cf;
+    uint64_t t = c.bid;
+    Tile cur{};
+    for (; t < total; t += c.nblk) {
+        cur = describe(t, cfi, cf);
+        if (cur.kind) break;
+    }
+    bool primed = false;
+    while (t < total) {
+        uint64_t tn = t + c.nblk;
+        Tile nxt{};
+        for (; tn < total; tn += c.nblk) {
+            nxt = describe(tn, cfi, cf);
+            if (nxt.kind) break;
+        }
+        if (cur.kind == 2) {
+            // nothing is in flight here: the tile before did not prefetch into a
+            // generic tile, and its own copies were all waited for
+            __syncthreads();
+            generic(c, cur);
+            __syncthreads();
+            primed = false;
+        } else {
+            const uint64_t ld = cur.nr;
+            const double* a_cur = cur.F + (uint64_t)(kb + aq) * ld + cur.i0 + ai;
+            const double* b_cur = cur.F + (uint64_t)(cur.j0 + bj) * ld + kb + bq;
+            double* c_cur = cur.F + (uint64_t)cur.j0 * ld + cur.i0;
+            const bool pf = tn < total && nxt.kind == 1;
+            const uint64_t ldn = nxt.nr;
+            const double* a_nxt = nxt.F + (uint64_t)(kb + aq) * ldn + nxt.i0 + ai;
+            const double* b_nxt = nxt.F + (uint64_t)(nxt.j0 + bj) * ldn + kb + bq;
+            const double* c_nxt = nxt.F + (uint64_t)(nxt.j0 + aq) * ldn + nxt.i0 + ai;
+            if (!primed) {
+                const double* cs = c_cur + (uint64_t)aq * ld + ai;
+#pragma unroll 8
+                for (int it = 0; it < P::C_IT; ++it) {
+                    cp8(cdst0 + (uint32_t)(it * 2 * LDC) * 8u, cs);
+                    cs += 2 * ld;
+                }
+                const double* a = a_cur;
+#pragma unroll
+                for (int it = 0; it < P::A_IT; ++it) {
+                    cp8(adst0 + (uint32_t)(it * 2 * LDA) * 8u, a);
+                    a += 2 * ld;
+                }
+                const double* b = b_cur;
+#pragma unroll
+                for (int it = 0; it < P::B_IT; ++it) {
+                    cp8(bdst0 + (uint32_t)(it * 16 * LDB) * 8u, b);
+                    b += 16 * ld;
+                }
+                commit();
+            }
+            wait_all();
+            __syncthreads();
+            double acc[MT][NT][2];
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt)
+                        acc[mt][nt][h] = -Cs0[(nt * 8 + h) * LDC + mt * 8];
+            __syncthreads();  // the C buffer may be refilled from here on
+            uint32_t cn_dst = cdst0;
+#pragma unroll 1
+            for (int kc = 0; kc < NCHUNK; ++kc) {
+                if (kc) {
+                    wait_all();
+                    __syncthreads();
+                }
+                // what is staged during this chunk: chunk kc + 1 of this tile, or
+                // chunk 0 of the next one
+                const bool last = kc + 1 == NCHUNK;
+                const bool do_stage = !last || pf;
+                const uint64_t sld = last ? ldn : ld;
+                const double* sa = last ? a_nxt : a_cur + (uint64_t)((kc + 1) * WK) * ld;
+                const double* sb = last ? b_nxt : b_cur + (kc + 1) * WK;
+                const uint32_t sbuf = (uint32_t)((kc + 1) & 1) * STAGE_BYTES;
+                const double* As = As0 + (size_t)(kc & 1) * P::STAGE_DOUBLES;
+                const double* Bs = Bs0 + (size_t)(kc & 1) * P::STAGE_DOUBLES;
+#pragma unroll
+                for (int ks = 0; ks < P::KS; ++ks) {
+                    double a[MT], b[NT];
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt) a[mt] = As[ks * 4 * LDA + mt * 8];
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) b[nt] = Bs[nt * 8 * LDB + ks * 4];
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt) {
+#pragma unroll
+                        for (int nt = 0; nt < NT; ++nt) {
+                            asm volatile(
+                                    "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 "
+                                    "{%0,%1}, {%2}, {%3}, {%0,%1};"
+                                    : "+d"(acc[mt][nt][0]), "+d"(acc[mt][nt][1])
+                                    : "d"(a[mt]), "d"(b[nt]));
+                        }
+                    }
+                    if (ks == 0) {
+                        if (do_stage) {
+#pragma unroll
+                            for (int it = 0; it < P::A_IT; ++it) {
+                                cp8(adst0 + sbuf + (uint32_t)(it * 2 * LDA) * 8u, sa);
+                                sa += 2 * sld;
+                            }
+                        }
+                    } else if (ks == 1) {
+                        if (do_stage) {
+#pragma unroll
+                            for (int it = 0; it < P::B_IT; ++it) {
+                                cp8(bdst0 + sbuf + (uint32_t)(it * 16 * LDB) * 8u, sb);
+                                sb += 16 * sld;
+                            }
+                        }
+                        // this group: the stage above + the C copies of the chunk
+                        // before, which so get a whole chunk to arrive
+                        commit();
+                    } else if (pf) {
+                        // next tile's C: 64 copies per thread, 4 per slot
+#pragma unroll
+                        for (int it = 0; it < P::C_IT / (2 * NCHUNK); ++it) {
+                            cp8(cn_dst, c_nxt);
+                            c_nxt += 2 * ldn;
+                            cn_dst += (uint32_t)(2 * LDC) * 8u;
+                        }
+                    }
+                }
+            }
+            commit();
+            double* cst = c_cur + (uint64_t)(wn * (NT * 8) + 2 * t4) * ld + wm * (MT * 8) + g;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    double* col = cst + (uint64_t)(nt * 8 + h) * ld;
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt) __stcg(col + mt * 8, -acc[mt][nt][h]);
+                }
+            primed = pf;
+        }
+        t = tn;
+        cur = nxt;
+    }
+}
 #endif
 
 //! ROW: R' = D (P_r R) on one 128-column tile; COL: C' = -C D on one 128-row tile
