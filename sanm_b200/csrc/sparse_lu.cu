@@ -119,14 +119,48 @@ struct AssembleChildren {
         p.f = fronts[p.tk.front];
         return p;
     }
+    //! what an entry needs of a child: kept in shared memory for the block
+    //! instead of re-reading the 100-byte front descriptor per entry and child
+    struct ChildD {
+        const double* U;  //!< update block: U[jj * nr + ii]
+        const int32_t* inv;
+        uint32_t nr;
+    };
+    static constexpr uint32_t MAX_CH = 16;
     SANM_D void operator()(const rt::BlockCtx& c, const Pre& p) const {
         const Task tk = p.tk;
         const FrontD& f = p.f;
         const uint64_t total = (uint64_t)f.nr * f.nr;
         const uint64_t e0 = (uint64_t)tk.chunk * ASM_TILE;
         const uint64_t e1 = e0 + ASM_TILE < total ? e0 + ASM_TILE : total;
+        const uint32_t nch = f.child_end - f.child_begin;
+        if (nch <= MAX_CH) {
+            ChildD* ch = reinterpret_cast<ChildD*>(c.smem);
+            for (uint32_t q = c.tid; q < nch; q += c.nthr) {
+                const FrontD d = fronts[child_list[f.child_begin + q]];
+                ch[q] = ChildD{d.F + (uint64_t)d.nc * d.nr + d.nc, d.inv, d.nr};
+            }
+            c.sync();
+            for (uint64_t e = e0 + c.tid; e < e1; e += c.nthr) {
+                const uint32_t e32 = (uint32_t)e;  // nr^2 < 2^32 (checked at analysis)
+                const uint32_t i = e32 % f.nr, j = e32 / f.nr;
+                double acc = 0;
+                bool any = false;
+                for (uint32_t q = 0; q < nch; ++q) {
+                    // child order: the sum is the one of the plain loop below
+                    const int32_t ii = ch[q].inv[i], jj = ch[q].inv[j];
+                    if (ii >= 0 && jj >= 0) {
+                        acc += ch[q].U[(uint64_t)jj * ch[q].nr + ii];
+                        any = true;
+                    }
+                }
+                // entries no child reaches are not touched (no read-modify-write)
+                if (any) f.F[e] += acc;
+            }
+            return;
+        }
         for (uint64_t e = e0 + c.tid; e < e1; e += c.nthr) {
-            const uint32_t e32 = (uint32_t)e;  // nr <= 13000: fits
+            const uint32_t e32 = (uint32_t)e;
             const uint32_t i = e32 % f.nr, j = e32 / f.nr;
             double acc = 0;
             for (uint32_t q = f.child_begin; q < f.child_end; ++q) {
@@ -1359,7 +1393,8 @@ void SparseLU::factor(const double* vals_dev) {
     for (auto& L : T.levels) {
         if (L.asm_n) {
             LuScope ps{"lu_asm"};
-            rt::for_each_block<256>(L.asm_n, 256, 0,
+            rt::for_each_block<256>(L.asm_n, 256,
+                               AssembleChildren::MAX_CH * sizeof(AssembleChildren::ChildD),
                                AssembleChildren{I.fd.ptr(), T.child_list.ptr(),
                                                 T.asm_tasks.ptr() + L.asm_off});
         }
