@@ -1103,6 +1103,10 @@ struct LuTopo {
         uint32_t prep_off = 0, prep_n = 0;    //!< (front, 256-row chunk) tasks
         uint32_t fwd_off = 0, fwd_n = 0, bwd_off = 0, bwd_n = 0;
         uint32_t max_nc = 0, max_nr = 0;
+        //! the level's tasks are ordered narrow fronts first (forward: nc, backward:
+        //! nr below SOLVE_WIDE_COLS): [off, off + split) can run in narrow blocks
+        uint32_t fwd_split = 0, bwd_split = 0;
+        uint32_t fwd_narrow_nc = 0, bwd_narrow_nr = 0;  //!< maxima over the narrow part
     };
     std::vector<Level> levels;
     rt::DBuf<Task> asm_tasks, fwd_tasks, bwd_tasks;
@@ -1285,12 +1289,28 @@ void SparseLU::analyze(uint64_t n, const uint32_t* rowptr,
                 L.big_max_nc = std::max(L.big_max_nc, nc);
                 L.big_max_nr = std::max(L.big_max_nr, nr);
             }
-            uint32_t nf = std::max<uint32_t>(1, (nu + FWD_ROWS - 1) / FWD_ROWS);
-            for (uint32_t t = 0; t < nf; ++t) fwd_t.push_back({s, t});
-            uint32_t nbk = (nc + BWD_ROWS - 1) / BWD_ROWS;
-            for (uint32_t t = 0; t < nbk; ++t) bwd_t.push_back({s, t});
             L.max_nc = std::max(L.max_nc, nc);
             L.max_nr = std::max(L.max_nr, nr);
+        }
+        for (int pass = 0; pass < 2; ++pass) {
+            for (uint32_t q = S.level_ptr[l]; q < S.level_ptr[l + 1]; ++q) {
+                const uint32_t s = S.level_list[q];
+                const uint32_t nr = S.sn_nr[s], nc = S.sn_nc[s], nu = nr - nc;
+                if ((nc < SOLVE_WIDE_COLS) == (pass == 0)) {
+                    uint32_t nf = std::max<uint32_t>(1, (nu + FWD_ROWS - 1) / FWD_ROWS);
+                    for (uint32_t t = 0; t < nf; ++t) fwd_t.push_back({s, t});
+                    if (pass == 0) L.fwd_narrow_nc = std::max(L.fwd_narrow_nc, nc);
+                }
+                if ((nr < SOLVE_WIDE_COLS) == (pass == 0)) {
+                    uint32_t nbk = (nc + BWD_ROWS - 1) / BWD_ROWS;
+                    for (uint32_t t = 0; t < nbk; ++t) bwd_t.push_back({s, t});
+                    if (pass == 0) L.bwd_narrow_nr = std::max(L.bwd_narrow_nr, nr);
+                }
+            }
+            if (pass == 0) {
+                L.fwd_split = (uint32_t)fwd_t.size() - L.fwd_off;
+                L.bwd_split = (uint32_t)bwd_t.size() - L.bwd_off;
+            }
         }
         L.asm_n = (uint32_t)asm_t.size() - L.asm_off;
         L.small_n = (uint32_t)small_l.size() - L.small_off;
@@ -1626,6 +1646,13 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
     }
     char tag[32];
     static const bool no_hoist = getenv("SANM_LU_NO_HOIST") != nullptr;
+    // narrow tasks of a mixed level get their own launch from this many on
+    // (SANM_LU_SOLVE_SPLIT; 0 = never)
+    static const uint32_t split_min = [] {
+        const char* e = getenv("SANM_LU_SOLVE_SPLIT");
+        const int v = e ? atoi(e) : 4096;
+        return v > 0 ? (uint32_t)v : 0xFFFFFFFFu;
+    }();
     for (auto& L : T.levels) {
         snprintf(tag, sizeof(tag), "lu_fwd_%02d", (int)(&L - T.levels.data()));
         LuScope ps{tag};
@@ -1646,12 +1673,26 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
                                               T.fwd_tasks.ptr() + L.fwd_off, b_dev,
                                               T.perm.ptr(), 0});
         } else if (L.max_nc >= SOLVE_WIDE_COLS) {
+            // a large level that mixes wide and narrow fronts (the bottom of a
+            // big problem): the narrow ones in narrow blocks, as their own launch
+            uint32_t skip = 0;
+            if (L.fwd_split >= split_min && L.fwd_split < L.fwd_n) {
+                constexpr int G = FWD_GROUPS_NARROW;
+                skip = L.fwd_split;
+                rt::for_each_block<R * G>(
+                        skip, R * G,
+                        (2 * (size_t)L.fwd_narrow_nc + solve_scratch_doubles<R, G>()) *
+                                sizeof(double),
+                        ForwardKernel<R, G>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
+                                            T.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                            T.perm.ptr(), hoist});
+            }
             constexpr int G = FWD_GROUPS_WIDE;
             rt::for_each_block<R * G>(
-                    L.fwd_n, R * G,
+                    L.fwd_n - skip, R * G,
                     (2 * (size_t)L.max_nc + solve_scratch_doubles<R, G>()) * sizeof(double),
                     ForwardKernel<R, G>{I.fd.ptr(), T.gsrc.ptr(), I.vecs.ptr(),
-                                     T.fwd_tasks.ptr() + L.fwd_off, b_dev,
+                                     T.fwd_tasks.ptr() + L.fwd_off + skip, b_dev,
                                      T.perm.ptr(), hoist});
         } else {
             constexpr int G = FWD_GROUPS_NARROW;
@@ -1682,11 +1723,22 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
                     BackwardKernel<R, G, true>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
                                                I.xp.ptr(), x_dev, T.perm.ptr(), 0});
         } else if (L.max_nr >= SOLVE_WIDE_COLS) {
+            uint32_t skip = 0;
+            if (L.bwd_split >= split_min && L.bwd_split < L.bwd_n) {
+                constexpr int G = BWD_GROUPS_NARROW;
+                skip = L.bwd_split;
+                rt::for_each_block<R * G>(
+                        skip, R * G,
+                        ((size_t)L.bwd_narrow_nr + solve_scratch_doubles<R, G>()) *
+                                sizeof(double),
+                        BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
+                                             I.xp.ptr(), x_dev, T.perm.ptr(), hoist});
+            }
             constexpr int G = BWD_GROUPS_WIDE;
             rt::for_each_block<R * G>(
-                    L.bwd_n, R * G,
+                    L.bwd_n - skip, R * G,
                     ((size_t)L.max_nr + solve_scratch_doubles<R, G>()) * sizeof(double),
-                    BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off,
+                    BackwardKernel<R, G>{I.fd.ptr(), T.bwd_tasks.ptr() + L.bwd_off + skip,
                                       I.xp.ptr(), x_dev, T.perm.ptr(), hoist});
         } else {
             constexpr int G = BWD_GROUPS_NARROW;
