@@ -194,20 +194,47 @@ FusedKAssembly::HostLists FusedKAssembly::build_host(
     }
     lap("dloc (parallel)");
     if (bad) return out;
-    // source lists per destination, ascending (tet, local entry): a counting
-    // sort, parallel over destination ranges (every thread scans all of dloc
-    // and keeps what falls into its range, so the order inside a list is the
-    // scan order whatever the thread count)
+    // source lists per destination, ascending (tet, local entry).  Bucketed
+    // counting sort: every thread walks its own tet range once and files its
+    // (destination, source) pairs by destination range; then every range is
+    // counted and filled from the files in thread order = tet order.  The order
+    // inside a list is the tet order whatever the thread count.
     const uint64_t nd = nnz + n;
     std::vector<uint32_t> kptr(nd + 1, 0);
     const int T = rt::host_threads();
+    struct Pair {
+        uint32_t d, src;
+    };
+    std::vector<std::vector<Pair>> files((size_t)T * T);  // [walker * T + range]
+    auto range_of = [nd, T](uint32_t d) { return (int)((uint64_t)d * T / nd); };
 #pragma omp parallel num_threads(T)
     {
         const int t = omp_get_thread_num(), nt = omp_get_num_threads();
-        const uint32_t d0 = (uint32_t)(nd * t / nt), d1 = (uint32_t)(nd * (t + 1) / nt);
-        for (size_t i = 0; i < dloc.size(); ++i) {
-            const uint32_t d = dloc[i];
-            if (d >= d0 && d < d1) ++kptr[d + 1];  // NONE32 is out of every range
+        // (nt == T: the team size was requested explicitly; fewer threads still
+        // work, each one walks several tet ranges)
+        for (int w = t; w < T; w += nt) {
+            const uint64_t e0 = N * w / T, e1 = N * (w + 1) / T;
+            std::vector<Pair>* mine = files.data() + (size_t)w * T;
+            for (int r = 0; r < T; ++r) mine[r].reserve((e1 - e0) * 40 / T + 16);
+            for (uint64_t e = e0; e < e1; ++e) {
+                const uint32_t* row = dloc.data() + (size_t)e * KE_ENTRIES;
+                for (int l = 0; l < KE_ENTRIES; ++l) {
+                    const uint32_t d = row[l];
+                    if (d == NONE32) continue;
+                    mine[range_of(d)].push_back(
+                            Pair{d, (uint32_t)((uint64_t)l * npad + e)});
+                }
+            }
+        }
+    }
+    lap("file by range");
+#pragma omp parallel num_threads(T)
+    {
+        const int t = omp_get_thread_num(), nt = omp_get_num_threads();
+        for (int r = t; r < T; r += nt) {
+            for (int w = 0; w < T; ++w) {
+                for (const Pair& p : files[(size_t)w * T + r]) ++kptr[p.d + 1];
+            }
         }
     }
     lap("count");
@@ -218,12 +245,9 @@ FusedKAssembly::HostLists FusedKAssembly::build_host(
 #pragma omp parallel num_threads(T)
         {
             const int t = omp_get_thread_num(), nt = omp_get_num_threads();
-            const uint32_t d0 = (uint32_t)(nd * t / nt), d1 = (uint32_t)(nd * (t + 1) / nt);
-            for (uint64_t e = 0; e < N; ++e) {
-                const uint32_t* row = dloc.data() + (size_t)e * KE_ENTRIES;
-                for (int l = 0; l < KE_ENTRIES; ++l) {
-                    const uint32_t d = row[l];
-                    if (d >= d0 && d < d1) ksrc[fill[d]++] = (uint32_t)((uint64_t)l * npad + e);
+            for (int r = t; r < T; r += nt) {
+                for (int w = 0; w < T; ++w) {
+                    for (const Pair& p : files[(size_t)w * T + r]) ksrc[fill[p.d]++] = p.src;
                 }
             }
         }
