@@ -156,7 +156,7 @@ void dzero(void* dst, size_t bytes) {
 }
 
 namespace {
-cudaStream_t g_pipe[3] = {nullptr, nullptr, nullptr};
+cudaStream_t g_pipe[4] = {nullptr, nullptr, nullptr, nullptr};
 cudaStream_t pipe_stream(int pipe) {
     check_device();
     if (!g_pipe[pipe]) {

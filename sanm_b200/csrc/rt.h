@@ -165,6 +165,8 @@ constexpr int PIPE_H2D = 0, PIPE_D2H = 1;
 //! third side stream: exchange steps (comm.cu) that run beside the element
 //! kernels of the next order
 constexpr int PIPE_COMM = 2;
+//! side stream of the factorisation's look-ahead (sparse_lu.cu)
+constexpr int PIPE_AUX = 3;
 //! while alive, stream() is the given pipe: kernels and collectives launched
 //! in the scope go to the side stream (the caller orders it with fences)
 struct ScopedPipe {

@@ -595,6 +595,9 @@ struct WideGemmPersistKernel {
     const FrontD* fronts;
     const uint32_t* list;
     uint32_t kb, tiles, nfront;
+    //! the tile of the NEXT pivot block was updated by WidePivotTileKernel and is
+    //! being inverted on the side stream while this kernel runs: not touched here
+    int skip_next_pivot;
 
     struct Tile {
         int kind;  //!< 0 nothing to do, 1 interior (fast), 2 generic
@@ -616,6 +619,7 @@ struct WideGemmPersistKernel {
         d.j0 = (idx / tiles) * WT;
         d.kind = 0;
         if (kb >= d.nc || d.i0 >= d.nr || d.j0 >= d.nr) return d;
+        if (skip_next_pivot && d.i0 == kb + WB && d.j0 == kb + WB && kb + WB < d.nc) return d;
         const uint32_t wb = d.nc - kb < (uint32_t)WB ? d.nc - kb : (uint32_t)WB;
         const uint32_t mi = d.nr - d.i0 < (uint32_t)WT ? d.nr - d.i0 : (uint32_t)WT;
         const uint32_t nj = d.nr - d.j0 < (uint32_t)WT ? d.nr - d.j0 : (uint32_t)WT;
@@ -821,6 +825,28 @@ SANM_D inline void WideGemmPersistKernel::operator()(const rt::BlockCtx& c) cons
     }
 }
 #endif
+
+/*! Look-ahead of the pivot-block inverse: the one trailing tile of step kb that
+ * holds the NEXT pivot block, updated ahead of the rest of the trailing
+ * update, so that WideDiagKernel(kb + WB) -- a single CTA per front, 0.19 ms,
+ * during which the other 147 SMs used to idle -- can run on a side stream
+ * beside the trailing update instead of after it.  Same tile function and
+ * operands as the trailing update: results do not change. */
+struct WidePivotTileKernel {
+    const FrontD* fronts;
+    const uint32_t* list;
+    uint32_t kb;
+    SANM_D FrontD pre(const rt::BlockCtx& c) const { return fronts[list[c.bid]]; }
+    SANM_D void operator()(const rt::BlockCtx& c, const FrontD& f) const {
+        const uint32_t p0 = kb + WB;
+        if (p0 >= f.nc) return;  // no next step for this front
+        const uint32_t ext = f.nr - p0 < (uint32_t)WT ? f.nr - p0 : (uint32_t)WT;
+        wide_gemm_tile<WideGemmBig, W_SUB>(c, f.F + (uint64_t)kb * f.nr + p0, f.nr,
+                                           f.F + (uint64_t)p0 * f.nr + kb, f.nr, nullptr,
+                                           f.F + (uint64_t)p0 * f.nr + p0, f.nr, ext, ext,
+                                           (uint32_t)WB, 0, 0, 0, 0);
+    }
+};
 
 //! ROW: R' = D (P_r R) on one 128-column tile; COL: C' = -C D on one 128-row tile
 template <bool ROW>

@@ -172,15 +172,22 @@ def test_wide_gemm_fast_tiles_bitwise_gpu(cuda_impl, monkeypatch):
     n = A.shape[0]
     b = rng.uniform(-1, 1, n)
     xs = []
-    for cfg, slow in (("big", False), ("big", True), ("persist", False)):
-        monkeypatch.setenv("SANM_LU_WIDE_CFG", cfg)
+    for cfg, slow in (("big", False), ("big", True), ("persist", False),
+                      ("persist+lookahead", False)):
+        monkeypatch.setenv("SANM_LU_WIDE_CFG", cfg.split("+")[0])
+        if "lookahead" in cfg:
+            monkeypatch.setenv("SANM_LU_LOOKAHEAD", "1")
+        else:
+            monkeypatch.delenv("SANM_LU_LOOKAHEAD", raising=False)
         if slow:
             monkeypatch.setenv("SANM_LU_WIDE_SLOW", "1")
         else:
             monkeypatch.delenv("SANM_LU_WIDE_SLOW", raising=False)
         xs.append(build(cuda_impl, A).prepare().solve(b))
-    # the persistent kernel (next tile's C prefetched into shared memory)
+    # the persistent kernel (next tile's C prefetched into shared memory), and
+    # with the pivot-block inverse of the next step on a side stream
     assert np.array_equal(xs[0], xs[2])
+    assert np.array_equal(xs[0], xs[3])
     assert np.array_equal(xs[0], xs[1])
     r = A @ xs[0] - b
     scale = abs(A).sum(axis=1).max() * np.abs(xs[0]).max() + np.abs(b).max()
