@@ -142,6 +142,38 @@ def test_wide_front_path(impl, shape, nonsym, monkeypatch):
         assert np.abs(x - xr).max() <= 1e-10 * np.abs(xr).max()
 
 
+def test_adjacency_fast_path_same_analysis(impl, monkeypatch):
+    """structurally symmetric patterns take their adjacency directly
+    (sparse_symbolic.cpp sym_adj_fast); the analysis and the solution must be
+    those of the general transposing build, and an unsymmetric pattern must
+    fall back to it"""
+    rng = np.random.default_rng(29)
+    A = grid_matrix(7, 6, 5, rng, nonsym=0.3)
+    n = A.shape[0]
+    b = rng.uniform(-1, 1, n)
+    res = []
+    # the topology cache is keyed by the pattern and would hide the second analysis
+    monkeypatch.setenv("SANM_NO_TOPO_CACHE", "1")
+    for general in (False, True):
+        if general:
+            monkeypatch.setenv("SANM_ND_NO_FAST_ADJ", "1")
+        else:
+            monkeypatch.delenv("SANM_ND_NO_FAST_ADJ", raising=False)
+        s = build(impl, A).prepare()
+        res.append((s.stats(), s.solve(b)))
+    assert res[0][0] == res[1][0]
+    assert np.array_equal(res[0][1], res[1][1])
+    # one-sided entries: the pattern is not symmetric any more
+    B = A.tolil()
+    B[0, n - 1] = 0.125
+    B[3, n - 2] = -0.25
+    B = B.tocsr()
+    monkeypatch.delenv("SANM_ND_NO_FAST_ADJ", raising=False)
+    x = build(impl, B).prepare().solve(b)
+    xr = spla.spsolve(B.tocsc(), b)
+    assert np.abs(x - xr).max() <= 1e-10 * np.abs(xr).max()
+
+
 @pytest.mark.gpu
 def test_large_system_gpu(cuda_impl, monkeypatch):
     """n = 140 k unknowns, nonsymmetric values: fronts of several thousand rows
