@@ -278,12 +278,16 @@ struct JacKernel {
         if (M::AUX) ld_strided<M::AUX>(aux, aux_ptr<M>(a, t));
         ld_soa<9>(dm, a.dminv, a.npad, t);
         double* jt = jac + t;
+        // unrolled: with a runtime j the unit tangent is indexed dynamically and
+        // lives in local memory (224-byte stack frame before)
+#pragma unroll
         for (int j = 0; j < 9; ++j) {
             const int r0 = j / 3, m0 = j % 3;
             double ts[S], Pt[9];
 #pragma unroll
             for (int q = 0; q < 9; ++q) ts[q] = 0;
             // d F[r0][c] / d Ds[r0][m0] = DmInv[m0][c]
+#pragma unroll
             for (int c = 0; c < 3; ++c) ts[r0 * 3 + c] = dm[m0 * 3 + c];
             M::tangent(ts, s0, aux, a.pr, ts, Pt);
 #pragma unroll
