@@ -1686,7 +1686,7 @@ void SparseLU::solve_once(double* x_dev, const double* b_dev) {
     static const bool no_hoist = getenv("SANM_LU_NO_HOIST") != nullptr;
     // narrow tasks of a mixed level get their own launch from this many on
     // (SANM_LU_SOLVE_SPLIT; 0 = never)
-    static const uint32_t split_min = [] {
+    const uint32_t split_min = [] {  // per call: tests switch it
         const char* e = getenv("SANM_LU_SOLVE_SPLIT");
         const int v = e ? atoi(e) : 4096;
         return v > 0 ? (uint32_t)v : 0xFFFFFFFFu;

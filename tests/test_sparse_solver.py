@@ -142,6 +142,28 @@ def test_wide_front_path(impl, shape, nonsym, monkeypatch):
         assert np.abs(x - xr).max() <= 1e-10 * np.abs(xr).max()
 
 
+def test_solve_split_levels(impl, monkeypatch):
+    """large mixed levels run their narrow fronts as a launch of their own
+    (SANM_LU_SOLVE_SPLIT), in narrow blocks -- another, equally fixed summation
+    tree for those fronts; forced onto a small system: same solution to
+    rounding, bitwise repeatable, same residual bar"""
+    rng = np.random.default_rng(31)
+    A = grid_matrix(12, 10, 9, rng, nonsym=0.2)
+    n = A.shape[0]
+    b = rng.uniform(-1, 1, n)
+    s = build(impl, A).prepare()
+    monkeypatch.setenv("SANM_LU_SOLVE_SPLIT", "0")
+    x0 = s.solve(b)
+    monkeypatch.setenv("SANM_LU_SOLVE_SPLIT", "1")
+    x1 = s.solve(b)
+    x2 = s.solve(b)
+    assert np.array_equal(x1, x2)
+    assert np.abs(x1 - x0).max() <= 1e-12 * np.abs(x0).max()
+    r = A @ x1 - b
+    scale = abs(A).sum(axis=1).max() * np.abs(x1).max() + np.abs(b).max()
+    assert np.abs(r).max() <= 1e-12 * scale
+
+
 def test_adjacency_fast_path_same_analysis(impl, monkeypatch):
     """structurally symmetric patterns take their adjacency directly
     (sparse_symbolic.cpp sym_adj_fast); the analysis and the solution must be
