@@ -1593,7 +1593,8 @@ void SparseLU::solve(double* x_dev, const double* b_dev) {
     Impl& I = *m_impl;
     sanm_check(I.factored, "solve() before factor()");
 #ifndef SANM_HOSTEMU
-    if (getenv("SANM_LU_SOLVE_BENCH") && !I.bench_done) {
+    static const bool solve_bench = getenv("SANM_LU_SOLVE_BENCH") != nullptr;  // diagnostic
+    if (solve_bench && !I.bench_done) {
         // diagnostic: is a solve bound by the host's launch rate or by the
         // device?  20 solves enqueued back to back (host time to enqueue vs
         // device time), then the same chain replayed from a CUDA graph
