@@ -1248,6 +1248,23 @@ const TensorND& TensorND::compute_batched_svd_w(TensorND& u, TensorND& s,
                 Vs[i * n + jj] = v[i * n + j];
             }
         }
+        // (u_j, v_j) is only defined up to a common sign, and the Jacobi sweeps
+        // can land on either one for nearby inputs (the rotation angle jumps
+        // where two column norms cross).  Fix it by the largest component of
+        // u_j, so that U is a continuous function of M (tests/tensor.cpp takes
+        // finite differences of it); W = U V^T does not depend on the choice.
+        for (size_t j = 0; j < n; ++j) {
+            size_t im = 0;
+            for (size_t i = 1; i < n; ++i)
+                if (std::fabs(U[i * n + j]) > std::fabs(U[im * n + j]))
+                    im = i;
+            if (U[im * n + j] < 0) {
+                for (size_t i = 0; i < n; ++i) {
+                    U[i * n + j] = -U[i * n + j];
+                    Vs[i * n + j] = -Vs[i * n + j];
+                }
+            }
+        }
         auto make_w = [&]() { gemm(W, U, Vs.data(), n, n, n, false, true, false); };
         make_w();
         if (require_rotation && det_general(W, n, tmp, piv) < 0) {

@@ -7,9 +7,10 @@ ANM solver / Pade / TensorND case of the reference runs through the C ABI.
   gpu      cxx/_build/gpu_tests on the B200 (built in the container by
            __graft_entry__.build(); the binary travels with the snapshot)
 
-`Tensor.SVD` is excluded: it calls three host-side SVD derivative routines of
-libsanm/tensor_svd.h whose counterparts here live on the device
-(cxx/tests_support.cpp); tests/ano.cpp is out of scope.
+All 36 test cases of the three files run.  `Tensor.SVD` calls three host-side
+SVD derivative routines of libsanm/tensor_svd.h whose counterparts on the GPU
+path live on the device; plain host versions for the test are in
+cxx/tests_support.cpp.  tests/ano.cpp is out of scope.
 """
 import os
 import subprocess
@@ -20,15 +21,14 @@ import pytest
 from conftest import HAS_CUDA, ROOT
 
 REF = "/root/reference"
-FILTER = "~Tensor.SVD"
-#: test cases of the three files minus Tensor.SVD
-NR_CASES = 35
+#: test cases of tests/symbolic.cpp + pade.cpp + tensor.cpp
+NR_CASES = 36
 
 
 def run_suite(binary, timeout):
     # the suite writes its convergence logs (log_det_*.txt ...) into the cwd
     with tempfile.TemporaryDirectory(prefix="ref_suite_") as cwd:
-        p = subprocess.run([binary, FILTER], stdout=subprocess.PIPE, cwd=cwd,
+        p = subprocess.run([binary], stdout=subprocess.PIPE, cwd=cwd,
                            stderr=subprocess.STDOUT, text=True, timeout=timeout)
     tail = "\n".join(p.stdout.splitlines()[-60:])
     assert p.returncode == 0, tail
